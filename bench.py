@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""bench.py -- quasars/sec of the DLA model-evaluation hot path on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One step = one pass of the hot path (K0 Phi table, K1 Voigt+weights, K2 DMMA contraction +
+Cholesky, K3 log-mean-exp/argmax) over one batch of synthetic quasars of BASELINE.json
+config-2 shape (1217 pixels, k = 20, S = 10000 hypotheses).  Quasars shard across ranks with
+no collective on the data path (weak scaling: --quasars per GPU per step).  Rank 0 prints ONE
+JSON line.  `value` is device-resident throughput (inputs already in HBM), `e2e` goes through
+dla_eval_batch with pinned HOST buffers (H2D + D2H inside the timed region).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "quasars/sec"
+N_PIX, K_RANK = 1217, 20
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--quasars", type=int, default=192, help="quasars per GPU per step")
+    ap.add_argument("--samples", type=int, default=10000, help="num_dla_samples (config 2: 10000)")
+    ap.add_argument("--cpu-baseline-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.gpu), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measure_dgemm_tflops(torch, n=8192, reps=5):
+    """FP64 tensor roofline denominator: cuBLAS DGEMM n^3, best of reps (MEASURED_PEAKS.json has none)."""
+    a = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    b = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    torch.matmul(a, b)
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); torch.matmul(a, b); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    torch.cuda.empty_cache()
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_rate(prepared, samples, seconds: float, nthreads: int = 0):
+    """Time the CPU implementation of the path on a bounded sample of the same workload:
+    voigt.c compiled verbatim (oracle/_ref) for the profile + the plain-C restatement of
+    process_qsos.m:184-209 / log_mvnpdf_low_rank.m as written, OpenMP over samples."""
+    from oracle import oracle as O
+    lib = O.load_c()
+    have_ref = O.load_ref() is not None
+    cores = nthreads if nthreads > 0 else lib.oracle_max_threads()
+    S = samples.offset_samples.shape[0]
+    p = prepared[0]
+    lp = (np.log(0.1), np.log(0.9))
+    n0 = min(S, 64 * cores)
+    t = time.perf_counter()
+    O.process_quasar_c(p, samples.offset_samples, samples.nhi_samples, *lp, use_ref_voigt=have_ref, nthreads=cores,
+                       first_sample=0, num_eval=n0)
+    dt0 = time.perf_counter() - t
+    n1 = int(min(S, max(n0, n0 * seconds / max(dt0, 1e-3))))
+    t = time.perf_counter()
+    O.process_quasar_c(p, samples.offset_samples, samples.nhi_samples, *lp, use_ref_voigt=have_ref, nthreads=cores,
+                       first_sample=0, num_eval=n1)
+    dt = time.perf_counter() - t
+    return {"value": (n1 / S) / dt, "unit": METRIC, "cores": cores,
+            "kind": "port",
+            "sample": f"{n1} of {S} hypotheses of 1 quasar ({N_PIX} px, k={K_RANK}) in {dt:.2f}s; "
+                      f"profile = {'reference voigt.c compiled verbatim' if have_ref else 'C restatement of voigt.c'}"
+                      f" + libcerf stand-in; log_mvnpdf_low_rank.m as written in C; OpenMP over samples"}, n1, dt
+
+
+def make_workload(args, rank):
+    from gp_dla_detection_b200 import synthetic
+    from gp_dla_detection_b200.process_qsos import PackedBatch, prepare_quasar
+    from gp_dla_detection_b200.set_parameters import Parameters
+    params = Parameters(k=K_RANK, num_dla_samples=args.samples)
+    model = synthetic.make_model(K_RANK, 0.25, 20260002, params)
+    samples = synthetic.make_samples(args.samples, params)
+    sp = synthetic.make_spectra(args.quasars, model, 20260002 + 1000 + rank, False, params)
+    prepared = [prepare_quasar(w, f, v, m, z, model, params)
+                for w, f, v, m, z in zip(sp.all_wavelengths, sp.all_flux, sp.all_noise_variance, sp.all_pixel_mask,
+                                         sp.z_qsos)]
+    return params, samples, sp, prepared, PackedBatch(prepared, K_RANK)
+
+
+def config_dict(args, world):
+    return {"workload": f"BASELINE config 2 shape (DR12Q-scale synthetic batch): {N_PIX} px, k={K_RANK}, "
+                        f"S={args.samples} hypotheses/quasar; {args.quasars} quasars per GPU per step, sharded by "
+                        f"quasar over {world} GPU(s), no collective; 162861 quasars = "
+                        f"{162861 / (args.quasars * world):.0f} such steps",
+            "quasars_per_gpu_per_step": args.quasars, "num_dla_samples": args.samples, "pixels": N_PIX, "k": K_RANK,
+            "l2": "per-step working set (W,U weight tiles, %.1f GB/GPU) far exceeds the 126 MB L2"
+                  % (args.quasars * 2 * 8 * 10048 * 1232 / 1e9)}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    world = args.gpus
+    params, samples, sp, prepared, batch = make_workload(argparse.Namespace(**{**vars(args), "quasars": 1}), 0)
+    per_step = max(2.0, min(30.0, 100.0 / max(1, args.steps + args.warmup)))
+    info, n1, _ = cpu_reference_rate(prepared, samples, per_step)
+    from oracle import oracle as O
+    have_ref = O.load_ref() is not None
+    S = args.samples
+    times = []
+    for it in range(args.warmup + args.steps):
+        t = time.perf_counter()
+        O.process_quasar_c(prepared[0], samples.offset_samples, samples.nhi_samples, np.log(0.1), np.log(0.9),
+                           use_ref_voigt=have_ref, nthreads=info["cores"], first_sample=0, num_eval=n1)
+        if it >= args.warmup:
+            times.append(time.perf_counter() - t)
+    total = sum(times)
+    value = (n1 / S) * args.steps / total
+    info["value"] = value
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_dict(args, world), "cpu_baseline": info,
+            "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference under Octave not runnable (no Octave/mkoctfile/libcerf); this arm times the "
+                    "reference's CPU algorithm: voigt.c verbatim + C restatement of the .m files, all host threads"}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    from gp_dla_detection_b200.process_qsos import DlaContext
+    params, samples, sp, prepared, batch = make_workload(args, rank)
+    S, Q = args.samples, batch.Q
+
+    # pinned host copies of the step inputs for the e2e leg
+    def pin(a):
+        t = torch.from_numpy(a).pin_memory()
+        return t.numpy(), t
+    keep = []
+    for name in ("pix_ptr", "pad_ptr", "padded_wavelengths", "profile_index", "flux", "mu", "omega2", "noise_variance",
+                 "M", "min_z_dla", "max_z_dla"):
+        arr, t = pin(getattr(batch, name))
+        setattr(batch, name, arr)
+        keep.append(t)
+
+    dgemm_tflops = measure_dgemm_tflops(torch)
+
+    ctx = DlaContext(k=K_RANK, num_lines=3, num_samples=S, device=local_rank, store_sample_ll=True)
+    ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+    ctx.stage(batch, sp.log_priors_dla, sp.log_priors_no_dla)
+
+    # ---- device-resident leg -----------------------------------------------------------------
+    for _ in range(args.warmup):
+        ctx.run_staged()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    ev_ms = {"ms_total": 0.0, "ms_phi": 0.0, "ms_voigt": 0.0, "ms_contract": 0.0, "ms_reduce": 0.0}
+    launches = 0
+    for _ in range(args.steps):
+        ctx.run_staged()
+        tm = ctx.timing()
+        for k_ in ev_ms:
+            ev_ms[k_] += tm[k_]
+        launches += tm["launches"]
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    dev_s = max_over_ranks(ev_ms["ms_total"] * 1e-3)   # CUDA events on the library's stream, max over ranks
+    wall_s = max_over_ranks(wall)
+    value = Q * world * args.steps / dev_s
+
+    # ---- end-to-end leg: dla_eval_batch, pinned host buffers in, host buffers out ---------------
+    outputs = ctx._alloc_outputs(Q)
+    ctx.eval_batch(batch, sp.log_priors_dla, sp.log_priors_no_dla, outputs)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = ctx.eval_batch(batch, sp.log_priors_dla, sp.log_priors_no_dla, outputs)
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    tm = ctx.timing()
+    e2e = {"value": Q * world * args.steps / e2e_s, "unit": METRIC, "h2d_bytes_per_step": int(tm["h2d_bytes"]),
+           "d2h_bytes_per_step": int(tm["d2h_bytes"]), "timed": "wall clock around K dla_eval_batch calls, max over ranks",
+           "host_prep": "per-quasar numpy preparation (process_qsos.m:102-180) is outside the timed region"}
+    assert np.all(np.isfinite(out["log_likelihoods_dla"]))
+
+    # ---- rooflines ------------------------------------------------------------------------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    n_sum = float(batch.n.sum())
+    flop_per_step = S * n_sum * K_RANK * (K_RANK + 3)            # n k (k+3) per (quasar, sample)
+    t_contract = ev_ms["ms_contract"] * 1e-3 / args.steps
+    t_voigt = ev_ms["ms_voigt"] * 1e-3 / args.steps
+    ach = flop_per_step / t_contract / 1e12
+    roofline = {"kernel": "contract_chol_kernel (K2: DMMA contraction + Cholesky epilogue)", "bound": "tensor",
+                "achieved": ach, "peak": dgemm_tflops, "unit": "TFLOP/s", "frac": ach / dgemm_tflops,
+                "traffic": None,
+                "peak_source": "FP64 tensor peak = cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json "
+                               "has no FP64 figure; the profiling guide states no FP64 fallback)",
+                "algorithmic_flop_per_launch": flop_per_step / max(1, tm["chunks"]),
+                "launches_per_step": int(tm["chunks"]), "ms_per_step": 1e3 * t_contract,
+                "step_frac_end_to_end": (flop_per_step / (dev_s / args.steps) / 1e12) / dgemm_tflops}
+    wu_bytes = 16.0 * S * n_sum                                    # W and U written once (fp64)
+    roofline_voigt = {"kernel": "voigt_weights_kernel (K1)", "bound": "fp64 vector pipe (reported vs hbm as north_star asks)",
+                      "achieved": wu_bytes / t_voigt / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                      "frac": wu_bytes / t_voigt / 1e9 / hbm_peak,
+                      "faddeeva_evals_per_s": 3.0 * S * float((batch.n_full + 6).sum()) / t_voigt,
+                      "ms_per_step": 1e3 * t_voigt,
+                      "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"}
+    dominant = "K1 voigt_weights_kernel" if t_voigt > t_contract else "K2 contract_chol_kernel"
+
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                cpu, _, _ = cpu_reference_rate(prepared, samples, args.cpu_baseline_seconds)
+            except Exception as e:  # the checker is optional for the product's own number
+                cpu = {"value": None, "unit": METRIC, "cores": 0, "kind": "port", "sample": f"failed: {e}"}
+        line = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": config_dict(args, world), "e2e": e2e, "gpu_launches": int(launches),
+                "clocks": clocks, "roofline": roofline, "roofline_voigt": roofline_voigt,
+                "dominant_kernel": dominant, "cpu_baseline": cpu,
+                "kernel_ms_per_step": {k_: v / args.steps for k_, v in ev_ms.items()},
+                "wall_ms_per_step": 1e3 * wall_s / args.steps,
+                "dr12q_projection_s": 162861 / value}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,590 @@
+// dla_b200.cu -- C ABI (include/dla_b200.h) and host orchestration of the sm_100a kernels.
+// No torch types, no CPU fallback: every compute entry point launches CUDA kernels.
+#include "../../include/dla_b200.h"
+
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+using dla::QuasarDesc;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct Chunk {
+  int q0, nq;
+  int64_t wu_doubles, bmat_doubles;
+  int max_npad, max_P;
+};
+
+// Device-side views of one staged batch.
+struct Inputs {
+  const QuasarDesc* desc;
+  const double *padded, *flux, *mu, *om, *nv, *M;
+  const int32_t* pidx;
+};
+
+}  // namespace
+
+struct dla_ctx {
+  int device = 0;
+  dla_params p{};
+  cudaStream_t stream = nullptr;
+  std::string err;
+  cudaEvent_t ev[8]{};
+  // hypothesis set
+  DevBuf d_offset, d_nhi;
+  bool have_samples = false;
+  // staged batch
+  int64_t Q = 0;
+  bool staged = false, ran = false;
+  std::vector<QuasarDesc> h_desc;
+  std::vector<Chunk> chunks;
+  DevBuf d_desc, d_padded, d_pidx, d_flux, d_mu, d_om, d_nv, d_M;
+  DevBuf d_sample_ll, d_ll_no, d_ll_dla, d_lp_no, d_lp_dla, d_post, d_map;
+  // chunk workspace
+  DevBuf d_W, d_U, d_bmat, d_aux, d_ll_chunk;
+  dla_timing timing{};
+};
+
+#define CU_TRY(ctx, call)                                                                          \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      char b_[512];                                                                                \
+      snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__,    \
+               __LINE__);                                                                          \
+      (ctx)->err = b_;                                                                             \
+      return e_ == cudaErrorMemoryAllocation ? DLA_ERR_OOM : DLA_ERR_CUDA;                         \
+    }                                                                                              \
+  } while (0)
+
+#define BAD_ARG(ctx, msg)       \
+  do {                          \
+    (ctx)->err = (msg);         \
+    return DLA_ERR_BAD_ARG;     \
+  } while (0)
+
+static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// ------------------------------------------------------------------------------------------
+// chunk execution
+// ------------------------------------------------------------------------------------------
+static int k1_warps_for(int raw_stride) {
+  const size_t budget = 200 * 1024;
+  int w = (int)(budget / ((size_t)raw_stride * 8));
+  if (w > dla::K1_THREADS / 32) w = dla::K1_THREADS / 32;
+  return w;
+}
+
+// Runs K0..K3 for one chunk of quasars on ctx->stream. sample_ll_chunk: [nq][S].
+static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S, int k, int num_lines,
+                        const double* d_offset, const double* d_nhi, double* sample_ll_chunk, double* ll_no,
+                        double* ll_dla, double* lp_no, double* lp_dla, double* post, int32_t* map_index,
+                        bool time_it) {
+  const int nsb = (int)((S + 1 + dla::TS - 1) / dla::TS);
+  double* W = c->d_W.as<double>();
+  double* U = c->d_U.as<double>();
+  double* B = c->d_bmat.as<double>();
+  double* aux = c->d_aux.as<double>();
+  cudaStream_t st = c->stream;
+  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[0], st));
+  {
+    dim3 grid((unsigned)(((int64_t)(ch.max_npad / 4) * dla::NCOL + 255) / 256), (unsigned)ch.nq);
+    dla::build_bmat_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.M, B, k);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[1], st));
+  {
+    const int raw_stride = (int)round_up(ch.max_P, 2);
+    const int warps = k1_warps_for(raw_stride);
+    if (warps < 1) BAD_ARG(c, "a quasar has too many padded pixels for the Voigt kernel's shared-memory row");
+    const size_t smem = (size_t)warps * raw_stride * 8;
+    dla::voigt_weights_kernel<<<(unsigned)((int64_t)ch.nq * nsb), warps * 32, smem, st>>>(
+        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pidx, in.flux, in.mu, in.om, in.nv, W, U, aux,
+        num_lines, raw_stride);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[2], st));
+  {
+    const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
+    dla::contract_chol_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K2_THREADS, smem, st>>>(
+        in.desc, ch.q0, nsb, S, W, U, B, aux, sample_ll_chunk, ll_no, k);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[3], st));
+  if (S > 0 && ll_dla) {
+    dla::reduce_kernel<<<(unsigned)ch.nq, 256, 0, st>>>(in.desc, ch.q0, S, sample_ll_chunk, ll_no, ll_dla, lp_no,
+                                                         lp_dla, post, map_index);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[4], st));
+  CU_TRY(c, cudaGetLastError());
+  if (time_it) {
+    CU_TRY(c, cudaEventSynchronize(c->ev[4]));
+    float ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[1])); c->timing.ms_phi += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[1], c->ev[2])); c->timing.ms_voigt += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[2], c->ev[3])); c->timing.ms_contract += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[3], c->ev[4])); c->timing.ms_reduce += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[4])); c->timing.ms_total += ms;
+  }
+  c->timing.launches += (S > 0 && ll_dla) ? 4 : 3;
+  return DLA_OK;
+}
+
+static int ensure_workspace(dla_ctx* c, int64_t wu_doubles, int64_t bmat_doubles, int nq, int64_t S, bool need_ll_chunk) {
+  const int64_t S_pad = round_up(S + 1, dla::TS);
+  CU_TRY(c, c->d_W.ensure((size_t)wu_doubles * 8));
+  CU_TRY(c, c->d_U.ensure((size_t)wu_doubles * 8));
+  CU_TRY(c, c->d_bmat.ensure((size_t)bmat_doubles * 8));
+  CU_TRY(c, c->d_aux.ensure((size_t)nq * 2 * S_pad * 8));
+  if (need_ll_chunk) CU_TRY(c, c->d_ll_chunk.ensure((size_t)std::max<int64_t>(1, (int64_t)nq * S) * 8));
+  return DLA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// ABI
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+int dla_abi_version(void) { return DLA_B200_ABI_VERSION; }
+
+int dla_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+const char* dla_last_error(const dla_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int dla_create(dla_ctx** out, int device, const dla_params* p) {
+  if (!out || !p) {
+    g_create_error = "dla_create: NULL argument";
+    return DLA_ERR_BAD_ARG;
+  }
+  *out = nullptr;
+  if (p->k < 1 || p->k > dla::KMAX) {
+    g_create_error = "dla_create: k must be in 1..20 (fused DMMA path)";
+    return DLA_ERR_BAD_ARG;
+  }
+  if (p->num_lines < 1 || p->num_lines > DLA_MAX_LINES) {
+    g_create_error = "dla_create: num_lines must be in 1..31 (voigt.c:16)";
+    return DLA_ERR_BAD_ARG;
+  }
+  if (p->num_samples < 0) {
+    g_create_error = "dla_create: num_samples < 0";
+    return DLA_ERR_BAD_ARG;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    g_create_error = std::string("dla_create: no CUDA device available (") +
+                     (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
+                     "); this library has no CPU fallback";
+    return DLA_ERR_NO_DEVICE;
+  }
+  if (device < 0 || device >= ndev) {
+    g_create_error = "dla_create: device index out of range";
+    return DLA_ERR_BAD_ARG;
+  }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major != 10) {
+    g_create_error = "dla_create: device is not sm_100 (kernels are built for sm_100a only)";
+    return DLA_ERR_NO_DEVICE;
+  }
+  dla_ctx* c = new dla_ctx();
+  c->device = device;
+  c->p = *p;
+  if (c->p.workspace_bytes <= 0) c->p.workspace_bytes = (int64_t)16 << 30;
+#define CREATE_TRY(call)                                                                   \
+  do {                                                                                     \
+    cudaError_t e2_ = (call);                                                              \
+    if (e2_ != cudaSuccess) {                                                              \
+      g_create_error = std::string("dla_create: " #call " failed: ") + cudaGetErrorString(e2_); \
+      delete c;                                                                            \
+      return DLA_ERR_CUDA;                                                                 \
+    }                                                                                      \
+  } while (0)
+  CREATE_TRY(cudaSetDevice(device));
+  CREATE_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (auto& ev : c->ev) CREATE_TRY(cudaEventCreate(&ev));
+  // per-line constants, computed as libcerf's voigt() does: (x + i gamma)/sqrt(2)/sigma, /sqrt(2 pi)/sigma
+  {
+    double gam[DLA_MAX_LINES], lc[DLA_MAX_LINES];
+    CREATE_TRY(cudaMemcpyFromSymbol(gam, dla_gammas, sizeof gam));
+    CREATE_TRY(cudaMemcpyFromSymbol(lc, dla_leading_constants, sizeof lc));
+    dla::LineConsts h;
+    const double sigma = DLA_SIGMA, s2pi = 2.50662827463100050242;
+    for (int j = 0; j < DLA_MAX_LINES; ++j) {
+      h.y[j] = gam[j] / sqrt(2.0) / sigma;
+      h.coef[j] = lc[j] / s2pi / sigma;
+      if (!(h.y[j] > DLA_FADD_YMIN && h.y[j] < DLA_FADD_YMAX)) {
+        g_create_error = "dla_create: Lorentz width outside the validated Faddeeva domain";
+        delete c;
+        return DLA_ERR_BAD_ARG;
+      }
+    }
+    h.inv_sqrt2_sigma = 1.0 / (sqrt(2.0) * sigma);
+    CREATE_TRY(cudaMemcpyToSymbol(dla::g_lines, &h, sizeof h));
+  }
+  CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
+  CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+#undef CREATE_TRY
+  *out = c;
+  return DLA_OK;
+}
+
+void dla_destroy(dla_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
+                    &c->d_nv, &c->d_M, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
+                    &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk})
+    b->release();
+  for (auto& ev : c->ev)
+    if (ev) cudaEventDestroy(ev);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+int dla_set_samples(dla_ctx* c, const double* offset_samples, const double* nhi_samples) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!offset_samples || !nhi_samples) BAD_ARG(c, "dla_set_samples: NULL pointer");
+  CU_TRY(c, cudaSetDevice(c->device));
+  const size_t bytes = (size_t)std::max<int64_t>(1, c->p.num_samples) * 8;
+  CU_TRY(c, c->d_offset.ensure(bytes));
+  CU_TRY(c, c->d_nhi.ensure(bytes));
+  if (c->p.num_samples > 0) {
+    CU_TRY(c, cudaMemcpyAsync(c->d_offset.p, offset_samples, (size_t)c->p.num_samples * 8, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(c->d_nhi.p, nhi_samples, (size_t)c->p.num_samples * 8, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+  }
+  c->have_samples = true;
+  return DLA_OK;
+}
+
+int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
+                    const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
+                    const double* mu, const double* omega2, const double* noise_variance, const double* M,
+                    const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
+                    const double* log_prior_no_dla) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  c->staged = false;
+  c->ran = false;
+  if (Q < 0 || Q > (int64_t)INT32_MAX) BAD_ARG(c, "dla_stage_batch: Q out of range");
+  if (!pix_ptr || !pad_ptr || !padded_wavelengths || !profile_index || !flux || !mu || !omega2 || !noise_variance ||
+      !M || !min_z_dla || !max_z_dla || !log_prior_dla || !log_prior_no_dla)
+    BAD_ARG(c, "dla_stage_batch: NULL input pointer");
+  if (!c->have_samples) {
+    c->err = "dla_stage_batch: dla_set_samples has not been called";
+    return DLA_ERR_STATE;
+  }
+  CU_TRY(c, cudaSetDevice(c->device));
+  const int64_t S = c->p.num_samples;
+  const int64_t S_pad = round_up(S + 1, dla::TS);
+  // descriptors + validation
+  c->h_desc.assign((size_t)Q, QuasarDesc{});
+  for (int64_t q = 0; q < Q; ++q) {
+    const int64_t n = pix_ptr[q + 1] - pix_ptr[q], P = pad_ptr[q + 1] - pad_ptr[q];
+    if (n < 0 || P < 7 || n > P - 6 || P > (1 << 24)) BAD_ARG(c, "dla_stage_batch: bad CSR (need 0 <= n_q <= P_q - 6)");
+    QuasarDesc& d = c->h_desc[(size_t)q];
+    d.pix_off = pix_ptr[q];
+    d.pad_off = pad_ptr[q];
+    d.n = (int32_t)n;
+    d.P = (int32_t)P;
+    d.npad = (int32_t)round_up(std::max<int64_t>(n, 1), dla::KC);
+    d.min_z = min_z_dla[q];
+    d.max_z = max_z_dla[q];
+    d.log_prior_dla = log_prior_dla[q];
+    d.log_prior_no_dla = log_prior_no_dla[q];
+    const int32_t* pi = profile_index + pix_ptr[q];
+    for (int64_t j = 0; j < n; ++j)
+      if (pi[j] < 0 || pi[j] > P - 7 || (j > 0 && pi[j] <= pi[j - 1]))
+        BAD_ARG(c, "dla_stage_batch: profile_index must be strictly increasing within [0, n_full)");
+  }
+  // chunk plan: split so that W+U of a chunk fit the workspace budget, chunks balanced
+  c->chunks.clear();
+  {
+    long double total = 0;
+    for (int64_t q = 0; q < Q; ++q) total += 16.0L * S_pad * c->h_desc[(size_t)q].npad;
+    const int64_t budget = c->p.workspace_bytes;
+    const int64_t nch = std::max<int64_t>(1, (int64_t)ceill(total / budget));
+    const long double target = total / nch;
+    int64_t q = 0;
+    while (q < Q) {
+      Chunk ch{(int)q, 0, 0, 0, 0, 0};
+      long double acc = 0;
+      while (q < Q) {
+        QuasarDesc& d = c->h_desc[(size_t)q];
+        const long double b = 16.0L * S_pad * d.npad;
+        if (ch.nq > 0 && (acc + b > budget || acc >= target)) break;
+        d.wu_off = ch.wu_doubles;
+        d.bmat_off = ch.bmat_doubles;
+        ch.wu_doubles += S_pad * d.npad;
+        ch.bmat_doubles += (int64_t)d.npad * dla::NCOL;
+        ch.max_npad = std::max(ch.max_npad, (int)d.npad);
+        ch.max_P = std::max(ch.max_P, (int)d.P);
+        acc += b;
+        ++ch.nq;
+        ++q;
+      }
+      c->chunks.push_back(ch);
+    }
+  }
+  const int64_t npix = pix_ptr[Q], npadtot = pad_ptr[Q];
+  const int k = c->p.k;
+  c->timing = dla_timing{};
+  CU_TRY(c, cudaEventRecord(c->ev[5], c->stream));
+  auto up = [&](DevBuf& b, const void* src, size_t bytes) -> cudaError_t {
+    cudaError_t e = b.ensure(std::max<size_t>(bytes, 16));
+    if (e != cudaSuccess || bytes == 0) return e;
+    c->timing.h2d_bytes += (int64_t)bytes;
+    return cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->stream);
+  };
+  CU_TRY(c, up(c->d_desc, c->h_desc.data(), (size_t)Q * sizeof(QuasarDesc)));
+  CU_TRY(c, up(c->d_padded, padded_wavelengths, (size_t)npadtot * 8));
+  CU_TRY(c, up(c->d_pidx, profile_index, (size_t)npix * 4));
+  CU_TRY(c, up(c->d_flux, flux, (size_t)npix * 8));
+  CU_TRY(c, up(c->d_mu, mu, (size_t)npix * 8));
+  CU_TRY(c, up(c->d_om, omega2, (size_t)npix * 8));
+  CU_TRY(c, up(c->d_nv, noise_variance, (size_t)npix * 8));
+  CU_TRY(c, up(c->d_M, M, (size_t)npix * k * 8));
+  CU_TRY(c, cudaEventRecord(c->ev[6], c->stream));
+  // outputs
+  const size_t q8 = (size_t)std::max<int64_t>(Q, 1) * 8;
+  if (c->p.store_sample_ll) CU_TRY(c, c->d_sample_ll.ensure(std::max<size_t>((size_t)Q * S * 8, 16)));
+  CU_TRY(c, c->d_ll_no.ensure(q8));
+  CU_TRY(c, c->d_ll_dla.ensure(q8));
+  CU_TRY(c, c->d_lp_no.ensure(q8));
+  CU_TRY(c, c->d_lp_dla.ensure(q8));
+  CU_TRY(c, c->d_post.ensure(2 * q8));
+  CU_TRY(c, c->d_map.ensure(q8));
+  // workspace for the largest chunk
+  {
+    int64_t wu = 0, bm = 0;
+    int nq = 0;
+    for (const Chunk& ch : c->chunks) {
+      wu = std::max(wu, ch.wu_doubles);
+      bm = std::max(bm, ch.bmat_doubles);
+      nq = std::max(nq, ch.nq);
+    }
+    int rc = ensure_workspace(c, std::max<int64_t>(wu, 2), std::max<int64_t>(bm, 2), std::max(nq, 1), S, !c->p.store_sample_ll);
+    if (rc != DLA_OK) return rc;
+  }
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  {
+    float ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]));
+    c->timing.ms_h2d = ms;
+  }
+  c->Q = Q;
+  c->staged = true;
+  return DLA_OK;
+}
+
+int dla_run_staged(dla_ctx* c) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!c->staged) {
+    c->err = "dla_run_staged: no batch staged";
+    return DLA_ERR_STATE;
+  }
+  CU_TRY(c, cudaSetDevice(c->device));
+  const int64_t S = c->p.num_samples;
+  const int64_t keep_h2d = c->timing.h2d_bytes;
+  const double keep_ms_h2d = c->timing.ms_h2d;
+  c->timing = dla_timing{};
+  c->timing.h2d_bytes = keep_h2d;
+  c->timing.ms_h2d = keep_ms_h2d;
+  Inputs in{c->d_desc.as<QuasarDesc>(), c->d_padded.as<double>(), c->d_flux.as<double>(), c->d_mu.as<double>(),
+            c->d_om.as<double>(), c->d_nv.as<double>(), c->d_M.as<double>(), c->d_pidx.as<int32_t>()};
+  for (const Chunk& ch : c->chunks) {
+    double* ll_chunk = c->p.store_sample_ll ? c->d_sample_ll.as<double>() + (int64_t)ch.q0 * S : c->d_ll_chunk.as<double>();
+    int rc = launch_chunk(c, in, ch, S, c->p.k, c->p.num_lines, c->d_offset.as<double>(), c->d_nhi.as<double>(), ll_chunk,
+                          c->d_ll_no.as<double>(), c->d_ll_dla.as<double>(), c->d_lp_no.as<double>(),
+                          c->d_lp_dla.as<double>(), c->d_post.as<double>(), c->d_map.as<int32_t>(), true);
+    if (rc != DLA_OK) return rc;
+    c->timing.chunks++;
+  }
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  c->ran = true;
+  return DLA_OK;
+}
+
+int dla_fetch_staged(dla_ctx* c, double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
+                     double* log_post_dla, double* model_posteriors, int32_t* map_index) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!c->ran) {
+    c->err = "dla_fetch_staged: dla_run_staged has not completed";
+    return DLA_ERR_STATE;
+  }
+  if (sample_ll && !c->p.store_sample_ll) BAD_ARG(c, "dla_fetch_staged: sample_ll requested but store_sample_ll = 0");
+  CU_TRY(c, cudaSetDevice(c->device));
+  const int64_t Q = c->Q, S = c->p.num_samples;
+  c->timing.d2h_bytes = 0;
+  CU_TRY(c, cudaEventRecord(c->ev[5], c->stream));
+  auto down = [&](void* dst, const DevBuf& b, size_t bytes) -> cudaError_t {
+    if (!dst || bytes == 0) return cudaSuccess;
+    c->timing.d2h_bytes += (int64_t)bytes;
+    return cudaMemcpyAsync(dst, b.p, bytes, cudaMemcpyDeviceToHost, c->stream);
+  };
+  CU_TRY(c, down(sample_ll, c->d_sample_ll, (size_t)Q * S * 8));
+  CU_TRY(c, down(ll_no_dla, c->d_ll_no, (size_t)Q * 8));
+  CU_TRY(c, down(ll_dla, c->d_ll_dla, (size_t)Q * 8));
+  CU_TRY(c, down(log_post_no_dla, c->d_lp_no, (size_t)Q * 8));
+  CU_TRY(c, down(log_post_dla, c->d_lp_dla, (size_t)Q * 8));
+  CU_TRY(c, down(model_posteriors, c->d_post, (size_t)Q * 16));
+  CU_TRY(c, down(map_index, c->d_map, (size_t)Q * 4));
+  CU_TRY(c, cudaEventRecord(c->ev[6], c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  float ms;
+  CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]));
+  c->timing.ms_d2h = ms;
+  return DLA_OK;
+}
+
+int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
+                   const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
+                   const double* mu, const double* omega2, const double* noise_variance, const double* M,
+                   const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
+                   const double* log_prior_no_dla, double* sample_ll, double* ll_no_dla, double* ll_dla,
+                   double* log_post_no_dla, double* log_post_dla, double* model_posteriors, int32_t* map_index) {
+  int rc = dla_stage_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2,
+                           noise_variance, M, min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
+  if (rc != DLA_OK) return rc;
+  rc = dla_run_staged(c);
+  if (rc != DLA_OK) return rc;
+  return dla_fetch_staged(c, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
+}
+
+int dla_get_timing(const dla_ctx* c, dla_timing* out) {
+  if (!c || !out) return DLA_ERR_BAD_ARG;
+  *out = c->timing;
+  return DLA_OK;
+}
+
+int dla_voigt(dla_ctx* c, const double* lambdas, int64_t num_points, double z, double N, int32_t num_lines,
+              double* profile) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!lambdas || !profile) BAD_ARG(c, "dla_voigt: NULL pointer");
+  if (num_points < 7 || num_points > (1 << 26)) BAD_ARG(c, "dla_voigt: need at least 7 points (voigt.c:271)");
+  if (num_lines <= 0 || num_lines > DLA_MAX_LINES) num_lines = DLA_MAX_LINES;  // voigt.c:266
+  CU_TRY(c, cudaSetDevice(c->device));
+  DevBuf lam, raw, prof;
+  int rc = DLA_OK;
+  auto fail = [&](cudaError_t e, const char* what) {
+    c->err = std::string("dla_voigt: ") + what + ": " + cudaGetErrorString(e);
+    rc = e == cudaErrorMemoryAllocation ? DLA_ERR_OOM : DLA_ERR_CUDA;
+  };
+  cudaError_t e;
+  if ((e = lam.ensure((size_t)num_points * 8)) != cudaSuccess) fail(e, "alloc");
+  if (rc == DLA_OK && (e = raw.ensure((size_t)num_points * 8)) != cudaSuccess) fail(e, "alloc");
+  if (rc == DLA_OK && (e = prof.ensure((size_t)num_points * 8)) != cudaSuccess) fail(e, "alloc");
+  if (rc == DLA_OK && (e = cudaMemcpyAsync(lam.p, lambdas, (size_t)num_points * 8, cudaMemcpyHostToDevice, c->stream)) != cudaSuccess)
+    fail(e, "h2d");
+  if (rc == DLA_OK) {
+    dla::voigt_single_kernel<<<1, 1024, 0, c->stream>>>(lam.as<double>(), (int)num_points, z, N, num_lines,
+                                                          raw.as<double>(), prof.as<double>());
+    if ((e = cudaGetLastError()) != cudaSuccess) fail(e, "launch");
+  }
+  if (rc == DLA_OK && (e = cudaMemcpyAsync(profile, prof.p, (size_t)(num_points - 6) * 8, cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess)
+    fail(e, "d2h");
+  if (rc == DLA_OK && (e = cudaStreamSynchronize(c->stream)) != cudaSuccess) fail(e, "sync");
+  lam.release();
+  raw.release();
+  prof.release();
+  return rc;
+}
+
+int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const double* M, const double* d,
+                            int64_t n, int32_t k, double* log_p) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!y || !mu || !M || !d || !log_p) BAD_ARG(c, "dla_log_mvnpdf_low_rank: NULL pointer");
+  if (n < 1 || n > (1 << 24)) BAD_ARG(c, "dla_log_mvnpdf_low_rank: n out of range");
+  if (k < 1 || k > dla::KMAX) BAD_ARG(c, "dla_log_mvnpdf_low_rank: k must be in 1..20");
+  CU_TRY(c, cudaSetDevice(c->device));
+  c->staged = false;  // reuses the chunk workspace
+  c->ran = false;
+  // One quasar, zero DLA samples: the no-DLA pseudo-sample (a == 1) with omega2 = 0 and
+  // noise_variance = d reproduces log N(y; mu, M M' + diag(d)) exactly.
+  QuasarDesc hd{};
+  hd.n = (int32_t)n;
+  hd.P = (int32_t)n + 6;
+  hd.npad = (int32_t)round_up(n, dla::KC);
+  Chunk ch{0, 1, (int64_t)dla::TS * hd.npad, (int64_t)hd.npad * dla::NCOL, hd.npad, hd.P};
+  int rc = ensure_workspace(c, ch.wu_doubles, ch.bmat_doubles, 1, 0, true);
+  if (rc != DLA_OK) return rc;
+  DevBuf dd, dy, dmu, dM, dzero, dnv, dout;
+  std::vector<double> zeros((size_t)n, 0.0);
+  auto cleanup = [&]() {
+    for (DevBuf* b : {&dd, &dy, &dmu, &dM, &dzero, &dnv, &dout}) b->release();
+  };
+#define SEAM_TRY(call)                                                                     \
+  do {                                                                                     \
+    cudaError_t e_ = (call);                                                               \
+    if (e_ != cudaSuccess) {                                                               \
+      c->err = std::string("dla_log_mvnpdf_low_rank: " #call ": ") + cudaGetErrorString(e_); \
+      cleanup();                                                                           \
+      return e_ == cudaErrorMemoryAllocation ? DLA_ERR_OOM : DLA_ERR_CUDA;                 \
+    }                                                                                      \
+  } while (0)
+  SEAM_TRY(dd.ensure(sizeof(QuasarDesc)));
+  SEAM_TRY(dy.ensure((size_t)n * 8));
+  SEAM_TRY(dmu.ensure((size_t)n * 8));
+  SEAM_TRY(dM.ensure((size_t)n * k * 8));
+  SEAM_TRY(dzero.ensure((size_t)n * 8));
+  SEAM_TRY(dnv.ensure((size_t)n * 8));
+  SEAM_TRY(dout.ensure(64));
+  SEAM_TRY(cudaMemcpyAsync(dd.p, &hd, sizeof hd, cudaMemcpyHostToDevice, c->stream));
+  SEAM_TRY(cudaMemcpyAsync(dy.p, y, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+  SEAM_TRY(cudaMemcpyAsync(dmu.p, mu, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+  SEAM_TRY(cudaMemcpyAsync(dM.p, M, (size_t)n * k * 8, cudaMemcpyHostToDevice, c->stream));
+  SEAM_TRY(cudaMemcpyAsync(dzero.p, zeros.data(), (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+  SEAM_TRY(cudaMemcpyAsync(dnv.p, d, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+  Inputs in{dd.as<QuasarDesc>(), dzero.as<double>(), dy.as<double>(), dmu.as<double>(), dzero.as<double>(),
+            dnv.as<double>(), dM.as<double>(), reinterpret_cast<const int32_t*>(dzero.p)};
+  rc = launch_chunk(c, in, ch, 0, k, 1, dzero.as<double>(), dzero.as<double>(), c->d_ll_chunk.as<double>(),
+                    dout.as<double>(), nullptr, nullptr, nullptr, nullptr, nullptr, false);
+  if (rc != DLA_OK) {
+    cleanup();
+    return rc;
+  }
+  SEAM_TRY(cudaMemcpyAsync(log_p, dout.p, 8, cudaMemcpyDeviceToHost, c->stream));
+  SEAM_TRY(cudaStreamSynchronize(c->stream));
+#undef SEAM_TRY
+  cleanup();
+  return DLA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,491 @@
+// kernels.cuh -- the four sm_100a kernels of the DLA model-evaluation hot path.
+//
+//   K0 build_bmat_kernel   per quasar: B = [vech(M_p M_p^T) | M_p] in DMMA-fragment order
+//   K1 voigt_weights_kernel  voigt.c:278-299 + process_qsos.m:163-165,:189-193: per (sample,pixel)
+//                            a, then w = a^2/d, u = a r/d written in DMMA-fragment order,
+//                            and the row reductions q0 = sum r^2/d, ld = sum log d
+//   K2 contract_chol_kernel  log_mvnpdf_low_rank.m:22-32 recast: G = W.Phi, v = U.M on FP64
+//                            tensor cores (DMMA.8x8x4), operands staged by 1-D TMA bulk copies
+//                            (cp.async.bulk + mbarrier), then the per-sample 20x20 Cholesky,
+//                            log-det and quadratic form in shared memory
+//   K3 reduce_kernel       process_qsos.m:202-212, :223-229, generate_ascii_catalog.m:73
+//
+// Geometry shared by all kernels (see DESIGN.md "Data layout in HBM"):
+//   TS  = 64 samples per sample block (one K2 CTA tile), KC = 16 pixels per K-chunk,
+//   NCOL = 240 B-columns = 27 tiles of 8 for vech(B) (210 used at k=20) + 3 tiles for M.
+//   W,U : [sample block][pixel/4][64 samples][4 pixels]   (an 8x4 DMMA A-fragment = 256 contiguous B)
+//   Bmat: [pixel/4][240 columns][4 pixels]                (a 4x8 DMMA B-fragment = 256 contiguous B)
+#ifndef GPDLA_KERNELS_CUH
+#define GPDLA_KERNELS_CUH
+
+#include <stdint.h>
+#include <cuda_runtime.h>
+#include "faddeeva.cuh"
+#include "faddeeva_table.cuh"
+#include "voigt_constants.cuh"
+
+namespace dla {
+
+constexpr int TS = 64;          // samples per sample block
+constexpr int KC = 16;          // pixels per K chunk
+constexpr int NT = 30;          // 8-column tiles per CTA
+constexpr int NCOL = NT * 8;    // 240
+constexpr int PHI_TILES = 27;   // tiles [0,27): vech(B)
+constexpr int VOFF = PHI_TILES * 8;  // 216: first column of v = U.M
+constexpr int KMAX = 20;
+constexpr int K2_THREADS = 256;
+constexpr int K2_STAGES = 4;
+constexpr int STAGE_W_DOUBLES = TS * KC;        // 1024
+constexpr int STAGE_B_DOUBLES = KC * NCOL;      // 3840
+constexpr int STAGE_DOUBLES = 2 * STAGE_W_DOUBLES + STAGE_B_DOUBLES;  // 5888 = 47104 B
+constexpr int LDC = NCOL + 2;   // epilogue row stride (doubles)
+constexpr int K1_THREADS = 512;
+constexpr double LOG_2PI = 1.83787706640934534;  // log_mvnpdf_low_rank.m:7
+
+// Per-line constants prepared on the host exactly as libcerf/voigt.c would:
+// y_j = gamma_j / sqrt(2) / sigma ; coef_j = leading_constants[j] / sqrt(2 pi) / sigma.
+struct LineConsts {
+  double y[DLA_MAX_LINES];
+  double coef[DLA_MAX_LINES];
+  double inv_sqrt2_sigma;  // 1 / (sqrt(2) sigma)
+};
+__device__ __constant__ LineConsts g_lines;
+
+// Per-quasar descriptor (device array, one per quasar of the staged batch).
+struct QuasarDesc {
+  int64_t pix_off;   // offset of this quasar in the per-kept-pixel arrays
+  int64_t pad_off;   // offset in padded_wavelengths
+  int64_t wu_off;    // offset (doubles) of W (and of U) in the chunk workspace
+  int64_t bmat_off;  // offset (doubles) of Bmat in the chunk workspace
+  int32_t n;         // kept pixels
+  int32_t P;         // padded points = n_full + 6
+  int32_t npad;      // n rounded up to KC
+  int32_t pad_;
+  double min_z, max_z;
+  double log_prior_dla, log_prior_no_dla;
+};
+
+// ----------------------------------------------------------------------------------------------
+// K0: Bmat[pc][col][kk] for pixel p = 4*pc + kk:
+//   col = i(i+1)/2 + l (l <= i < k): M[p,i]*M[p,l];  col = VOFF + i: M[p,i];  else 0;  p >= n: 0.
+// ----------------------------------------------------------------------------------------------
+__global__ void build_bmat_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ M,
+                                  double* __restrict__ bmat, int k) {
+  const QuasarDesc d = desc[q0 + blockIdx.y];
+  const int npc = d.npad / 4;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;  // (pc, col)
+  if (idx >= npc * NCOL) return;
+  const int pc = idx / NCOL, col = idx % NCOL;
+  int i = -1, l = -1;
+  if (col < k * (k + 1) / 2) {
+    i = (int)((sqrt(8.0 * col + 1.0) - 1.0) * 0.5);
+    while (i * (i + 1) / 2 > col) --i;
+    while ((i + 1) * (i + 2) / 2 <= col) ++i;
+    l = col - i * (i + 1) / 2;
+  } else if (col >= VOFF && col < VOFF + k) {
+    i = col - VOFF;
+  }
+  const double* Mq = M + (int64_t)k * d.pix_off;  // column-major n x k
+  double out[4];
+#pragma unroll
+  for (int kk = 0; kk < 4; ++kk) {
+    const int p = 4 * pc + kk;
+    double v = 0.0;
+    if (i >= 0 && p < d.n) {
+      const double mi = Mq[(int64_t)i * d.n + p];
+      v = (l >= 0) ? mi * Mq[(int64_t)l * d.n + p] : mi;
+    }
+    out[kk] = v;
+  }
+  double* dst = bmat + d.bmat_off + ((int64_t)pc * NCOL + col) * 4;
+  reinterpret_cast<double2*>(dst)[0] = make_double2(out[0], out[1]);
+  reinterpret_cast<double2*>(dst)[1] = make_double2(out[2], out[3]);
+}
+
+// ----------------------------------------------------------------------------------------------
+// K1: fused Voigt profile + instrument broadening + absorbed-model weights.
+// One warp per sample; raw profile of the sample kept in that warp's shared-memory row.
+// Sample index S is the no-DLA pseudo-sample (a == 1, process_qsos.m:150-152); samples > S
+// are padding of the last sample block and produce zeros.
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ double raw_transmission(double lambda, const double* mult, double N, int num_lines) {
+  // voigt.c:283-291
+  double total = 0.0;
+  for (int j = 0; j < num_lines; ++j) {
+    const double velocity = __dsub_rn(__dmul_rn(lambda, mult[j]), DLA_C_CGS);  // voigt.c:287, no FMA
+    const double x = velocity * g_lines.inv_sqrt2_sigma;
+    total -= g_lines.coef[j] * dla_re_w(x, g_lines.y[j], fadd_expa2n2);
+  }
+  return exp(N * total);
+}
+
+template <int NUM_LINES>
+__device__ __forceinline__ double raw_transmission_fixed(double lambda, const double* mult, double N) {
+  double total = 0.0;
+#pragma unroll
+  for (int j = 0; j < NUM_LINES; ++j) {
+    const double velocity = __dsub_rn(__dmul_rn(lambda, mult[j]), DLA_C_CGS);
+    const double x = velocity * g_lines.inv_sqrt2_sigma;
+    total -= g_lines.coef[j] * dla_re_w(x, g_lines.y[j], fadd_expa2n2);
+  }
+  return exp(N * total);
+}
+
+__global__ void __launch_bounds__(K1_THREADS, 1)
+voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
+                     const double* __restrict__ offset_samples, const double* __restrict__ nhi_samples,
+                     const double* __restrict__ padded_wavelengths, const int32_t* __restrict__ profile_index,
+                     const double* __restrict__ flux, const double* __restrict__ mu,
+                     const double* __restrict__ omega2, const double* __restrict__ noise_variance,
+                     double* __restrict__ Wbuf, double* __restrict__ Ubuf, double* __restrict__ aux,
+                     int num_lines, int raw_stride) {
+  extern __shared__ double k1_smem[];
+  const int ql = blockIdx.x / nsb, sb = blockIdx.x % nsb;
+  const QuasarDesc d = desc[q0 + ql];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = blockDim.x >> 5;
+  double* raw = k1_smem + (size_t)warp * raw_stride;
+
+  const double* lam = padded_wavelengths + d.pad_off;
+  const int32_t* pidx = profile_index + d.pix_off;
+  const double* y_ = flux + d.pix_off;
+  const double* mu_ = mu + d.pix_off;
+  const double* om_ = omega2 + d.pix_off;
+  const double* nv_ = noise_variance + d.pix_off;
+  const int npc = d.npad >> 2;
+  const int64_t S_pad = (int64_t)nsb * TS;
+  double* Wq = Wbuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
+  double* Uq = Ubuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
+  double* auxq = aux + (int64_t)ql * 2 * S_pad;
+
+  for (int srow = warp; srow < TS; srow += nwarps) {
+    const int64_t s = (int64_t)sb * TS + srow;
+    const bool phantom = s > S;
+    const bool no_dla = (s == S);
+    if (!phantom && !no_dla) {
+      // process_qsos.m:163-165: min + (max - min) * offset, separately rounded
+      const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), offset_samples[s]));
+      const double N = nhi_samples[s];
+      double mult[DLA_MAX_LINES];
+      if (num_lines == 3) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j)  // voigt.c:278-279
+          mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], __dadd_rn(1.0, z)) / 1e8;
+        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission_fixed<3>(lam[i], mult, N);
+      } else {
+        for (int j = 0; j < num_lines; ++j)
+          mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], __dadd_rn(1.0, z)) / 1e8;
+        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission(lam[i], mult, N, num_lines);
+      }
+    }
+    __syncwarp();
+    double q0acc = 0.0, ldacc = 0.0;
+    for (int j0 = 0; j0 < d.npad; j0 += 32) {
+      const int j = j0 + lane;
+      double w = 0.0, u = 0.0;
+      if (j < d.n && !phantom) {
+        double a = 1.0;
+        if (!no_dla) {
+          const double* rp = raw + pidx[j];
+          a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order, mul then add
+#pragma unroll
+          for (int t = 0; t < 7; ++t) a = __dadd_rn(a, __dmul_rn(rp[t], dla_instrument_profile[t]));
+        }
+        const double a2 = a * a;
+        const double dd = om_[j] * a2 + nv_[j];   // process_qsos.m:193, :197
+        const double r = y_[j] - mu_[j] * a;      // process_qsos.m:191, log_mvnpdf_low_rank.m:11
+        const double rinv = 1.0 / dd;             // log_mvnpdf_low_rank.m:13
+        w = a2 * rinv;
+        u = (a * r) * rinv;
+        q0acc += (r * r) * rinv;
+        ldacc += log(dd);
+      }
+      if (j < d.npad) {
+        const int64_t off = ((int64_t)(j >> 2) * TS + srow) * 4 + (j & 3);
+        Wq[off] = w;
+        Uq[off] = u;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      q0acc += __shfl_xor_sync(0xffffffffu, q0acc, o);
+      ldacc += __shfl_xor_sync(0xffffffffu, ldacc, o);
+    }
+    if (lane == 0) {
+      auxq[s] = q0acc;
+      auxq[S_pad + s] = ldacc;
+    }
+    __syncwarp();
+  }
+}
+
+// Single-profile seam (dla_voigt = the voigt MEX, voigt.c:253-304). One CTA.
+__global__ void voigt_single_kernel(const double* __restrict__ lambdas, int num_points, double z, double N,
+                                    int num_lines, double* __restrict__ raw, double* __restrict__ profile) {
+  __shared__ double mult[DLA_MAX_LINES];
+  if (threadIdx.x < num_lines)
+    mult[threadIdx.x] =
+        DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[threadIdx.x], __dadd_rn(1.0, z)) / 1e8;
+  __syncthreads();
+  for (int i = threadIdx.x; i < num_points; i += blockDim.x) raw[i] = raw_transmission(lambdas[i], mult, N, num_lines);
+  __syncthreads();
+  for (int i = threadIdx.x; i < num_points - 6; i += blockDim.x) {
+    double a = 0.0;
+#pragma unroll
+    for (int t = 0; t < 7; ++t) a = __dadd_rn(a, __dmul_rn(raw[i + t], dla_instrument_profile[t]));
+    profile[i] = a;
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// K2: DMMA contraction + Cholesky epilogue.
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  const uint32_t addr = smem_u32(bar);
+  uint32_t spins = 0;
+  do {
+    if (++spins > (1u << 28)) __trap();  // a lost bulk copy must fault, never hang the GPU
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+      : "+d"(c0), "+d"(c1)
+      : "d"(a), "d"(b));
+}
+
+// Packed lower-triangular index, row i >= column l.
+__device__ __forceinline__ int tri(int i, int l) { return ((i * (i + 1)) >> 1) + l; }
+
+// Per-sample epilogue on one row of the accumulator tile in shared memory, executed by a
+// quad (4 consecutive lanes). row[0..210): vech(G) (B = I + G), row[VOFF..VOFF+k): v.
+// Cholesky of the bordered matrix [[B, v],[v^T, q0]]: the border row ends as t = L^-1 v and
+// the corner as q0 - t^T t = r^T K^-1 r (log_mvnpdf_low_rank.m:24-32).  Returns log p on all
+// four lanes.
+__device__ __forceinline__ double chol_logp_quad(double* row, int k, int t, double q0, double ld, int n) {
+  double logdiag = 0.0;
+  double qq = q0;
+  const int vowner = k & 3;
+  // add the identity (log_mvnpdf_low_rank.m:23)
+  for (int i = t; i < k; i += 4) row[tri(i, i)] += 1.0;
+  __syncwarp();
+  for (int j = 0; j < k; ++j) {
+    const double djj = row[tri(j, j)];
+    const double ljj = sqrt(djj);
+    const double inv = 1.0 / ljj;
+    if ((j & 3) == t) logdiag += log(ljj);
+    // scale column j below the diagonal
+    int i0 = j + 1 + ((t - (j + 1)) & 3);
+    for (int i = i0; i < k; i += 4) row[tri(i, j)] *= inv;
+    if (t == vowner) row[VOFF + j] *= inv;
+    __syncwarp();
+    // trailing update
+    for (int i = i0; i < k; i += 4) {
+      const double lij = row[tri(i, j)];
+      double* ri = row + tri(i, 0);
+      for (int l = j + 1; l <= i; ++l) ri[l] -= lij * row[tri(l, j)];
+    }
+    if (t == vowner) {
+      const double vj = row[VOFF + j];
+      for (int l = j + 1; l < k; ++l) row[VOFF + l] -= vj * row[tri(l, j)];
+      qq -= vj * vj;
+    }
+    __syncwarp();
+  }
+  // combine across the quad
+  logdiag += __shfl_xor_sync(0xffffffffu, logdiag, 1);
+  logdiag += __shfl_xor_sync(0xffffffffu, logdiag, 2);
+  const int lane = threadIdx.x & 31;
+  qq = __shfl_sync(0xffffffffu, qq, (lane & ~3) | vowner);
+  // log_mvnpdf_low_rank.m:30-32
+  return -0.5 * (qq + (ld + 2.0 * logdiag) + (double)n * LOG_2PI);
+}
+
+__global__ void __launch_bounds__(K2_THREADS, 1)
+contract_chol_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
+                     const double* __restrict__ Wbuf, const double* __restrict__ Ubuf,
+                     const double* __restrict__ bmat, const double* __restrict__ aux,
+                     double* __restrict__ sample_ll /* [Qc][S] chunk-local */,
+                     double* __restrict__ ll_no_dla /* [Q] batch-global */, int k) {
+  extern __shared__ __align__(128) unsigned char k2_smem_raw[];
+  double* smem = reinterpret_cast<double*>(k2_smem_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)K2_STAGES * STAGE_DOUBLES);
+
+  const int ql = blockIdx.x / nsb, sb = blockIdx.x % nsb;
+  const QuasarDesc d = desc[q0 + ql];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int npc = d.npad >> 2;
+  const int nchunks = d.npad / KC;
+  const double* Wsrc = Wbuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
+  const double* Usrc = Ubuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
+  const double* Bsrc = bmat + d.bmat_off;
+
+  if (tid == 0) {
+    for (int s = 0; s < K2_STAGES; ++s) mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  auto issue = [&](int c) {
+    const int st = c % K2_STAGES;
+    double* dst = smem + (size_t)st * STAGE_DOUBLES;
+    mbar_expect_tx(&full[st], STAGE_DOUBLES * 8);
+    bulk_g2s(dst, Wsrc + (int64_t)c * STAGE_W_DOUBLES, STAGE_W_DOUBLES * 8, &full[st]);
+    bulk_g2s(dst + STAGE_W_DOUBLES, Usrc + (int64_t)c * STAGE_W_DOUBLES, STAGE_W_DOUBLES * 8, &full[st]);
+    bulk_g2s(dst + 2 * STAGE_W_DOUBLES, Bsrc + (int64_t)c * STAGE_B_DOUBLES, STAGE_B_DOUBLES * 8, &full[st]);
+  };
+  if (tid == 0) {
+    const int pre = nchunks < K2_STAGES ? nchunks : K2_STAGES;
+    for (int c = 0; c < pre; ++c) issue(c);
+  }
+
+  // warp tiling: 4 row groups of 16 samples x 2 column halves of 15 tiles
+  const int mrow = warp & 3, half = warp >> 2;
+  constexpr int TPW = NT / 2;  // 15 tiles per warp
+  double acc[TPW][4];
+#pragma unroll
+  for (int t = 0; t < TPW; ++t) acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.0;
+
+  for (int c = 0; c < nchunks; ++c) {
+    const int st = c % K2_STAGES;
+    mbar_wait(&full[st], (uint32_t)((c / K2_STAGES) & 1));
+    const double* Ws = smem + (size_t)st * STAGE_DOUBLES;
+    const double* Us = Ws + STAGE_W_DOUBLES;
+    const double* Bs = Us + STAGE_W_DOUBLES;
+#pragma unroll
+    for (int kc = 0; kc < KC / 4; ++kc) {
+      const double aw0 = Ws[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+      const double aw1 = Ws[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+      const double* bp = Bs + kc * (NCOL * 4) + (half * TPW) * 32 + lane;
+      if (half == 0) {
+#pragma unroll
+        for (int t = 0; t < TPW; ++t) {
+          const double b = bp[t * 32];
+          dmma884(acc[t][0], acc[t][1], aw0, b);
+          dmma884(acc[t][2], acc[t][3], aw1, b);
+        }
+      } else {
+        const double au0 = Us[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+        const double au1 = Us[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+#pragma unroll
+        for (int t = 0; t < TPW; ++t) {
+          const double b = bp[t * 32];
+          const bool isv = (TPW + t) >= PHI_TILES;  // compile-time per unrolled t
+          dmma884(acc[t][0], acc[t][1], isv ? au0 : aw0, b);
+          dmma884(acc[t][2], acc[t][3], isv ? au1 : aw1, b);
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && c + K2_STAGES < nchunks) issue(c + K2_STAGES);
+  }
+
+  // accumulators -> shared memory tile C[64][LDC] (the stage buffers are free now)
+  double* Cs = smem;
+  {
+    const int r0 = (2 * mrow) * 8 + (lane >> 2);
+    const int cbase = (half * TPW) * 8 + 2 * (lane & 3);
+#pragma unroll
+    for (int t = 0; t < TPW; ++t) {
+      double* p0 = Cs + (size_t)r0 * LDC + cbase + t * 8;
+      double* p1 = p0 + 8 * LDC;
+      p0[0] = acc[t][0]; p0[1] = acc[t][1];
+      p1[0] = acc[t][2]; p1[1] = acc[t][3];
+    }
+  }
+  __syncthreads();
+
+  // per-sample Cholesky / log-det / quadratic form: one quad per sample row
+  {
+    const int srow = tid >> 2, t = tid & 3;
+    const int64_t s = (int64_t)sb * TS + srow;
+    const int64_t S_pad = (int64_t)nsb * TS;
+    const double* auxq = aux + (int64_t)ql * 2 * S_pad;
+    const double q0v = auxq[s], ldv = auxq[S_pad + s];
+    const double lp = chol_logp_quad(Cs + (size_t)srow * LDC, k, t, q0v, ldv, d.n);
+    if (t == 0) {
+      if (s < S) sample_ll[(int64_t)ql * S + s] = lp;
+      else if (s == S) ll_no_dla[q0 + ql] = lp;
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// K3: per quasar log-mean-exp over samples, first-index argmax, posteriors.
+// process_qsos.m:202-212, :223-229; generate_ascii_catalog.m:73 (nanmax, first maximum wins).
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+reduce_kernel(const QuasarDesc* __restrict__ desc, int q0, int64_t S, const double* __restrict__ sample_ll,
+              const double* __restrict__ ll_no_dla, double* __restrict__ ll_dla, double* __restrict__ lp_no_dla,
+              double* __restrict__ lp_dla, double* __restrict__ model_post, int32_t* __restrict__ map_index) {
+  __shared__ double s_val[256];
+  __shared__ long long s_idx[256];
+  const int ql = blockIdx.x, tid = threadIdx.x;
+  const double* ll = sample_ll + (int64_t)ql * S;
+  // max ignoring NaN, first index
+  double best = 0.0;
+  long long bi = -1;
+  for (int64_t i = tid; i < S; i += 256) {
+    const double v = ll[i];
+    if (v != v) continue;
+    if (bi < 0 || v > best) { best = v; bi = i; }
+  }
+  s_val[tid] = best; s_idx[tid] = bi;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (tid < o) {
+      const double v2 = s_val[tid + o]; const long long i2 = s_idx[tid + o];
+      const double v1 = s_val[tid]; const long long i1 = s_idx[tid];
+      const bool take2 = (i2 >= 0) && (i1 < 0 || v2 > v1 || (v2 == v1 && i2 < i1));
+      if (take2) { s_val[tid] = v2; s_idx[tid] = i2; }
+    }
+    __syncthreads();
+  }
+  const double m = s_idx[0] >= 0 ? s_val[0] : __longlong_as_double(0x7ff8000000000000LL);
+  const long long mi = s_idx[0];
+  __syncthreads();
+  double acc = 0.0;
+  for (int64_t i = tid; i < S; i += 256) acc += exp(ll[i] - m);
+  s_val[tid] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (tid < o) s_val[tid] += s_val[tid + o];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int q = q0 + ql;
+    const QuasarDesc d = desc[q];
+    const double lld = m + log(s_val[0] / (double)S);  // :208-209
+    const double a = d.log_prior_no_dla + ll_no_dla[q];  // :154-155
+    const double b = d.log_prior_dla + lld;              // :211-212
+    ll_dla[q] = lld;
+    lp_no_dla[q] = a;
+    lp_dla[q] = b;
+    const double mx = (a > b || b != b) ? a : b;  // MATLAB max ignores NaN (:223-224)
+    const double ea = exp(a - mx), eb = exp(b - mx);
+    model_post[2 * q] = ea / (ea + eb);  // :226-229
+    model_post[2 * q + 1] = eb / (ea + eb);
+    map_index[q] = (int32_t)mi;
+  }
+}
+
+}  // namespace dla
+#endif

@@ -1,0 +1,37 @@
+/* oracle/shim/mex.h -- TEST INFRASTRUCTURE ONLY (not part of the product).
+ *
+ * A minimal stand-in for MATLAB/Octave's mex.h so that the reference's
+ * /root/reference/voigt.c can be compiled VERBATIM as plain C (no MATLAB, no
+ * Octave in this image).  It provides exactly the nine symbols voigt.c uses
+ * (voigt.c:253-277, :294, :301-302): mxArray, mwSize, mxREAL, mxGetPr,
+ * mxGetScalar, mxGetNumberOfElements, mxCreateDoubleMatrix (zero-initialised,
+ * which voigt.c:299's "+=" relies on), mxMalloc, mxFree.
+ */
+#ifndef ORACLE_SHIM_MEX_H
+#define ORACLE_SHIM_MEX_H
+#include <stddef.h>
+#include <stdlib.h>
+
+typedef size_t mwSize;
+typedef enum { mxREAL = 0, mxCOMPLEX = 1 } mxComplexity;
+
+typedef struct mxArray_shim {
+  double *pr;
+  mwSize m, n;
+} mxArray;
+
+static inline double *mxGetPr(const mxArray *a) { return a->pr; }
+static inline double mxGetScalar(const mxArray *a) { return a->pr[0]; }
+static inline mwSize mxGetNumberOfElements(const mxArray *a) { return a->m * a->n; }
+static inline mxArray *mxCreateDoubleMatrix(mwSize m, mwSize n, mxComplexity c) {
+  (void)c;
+  mxArray *a = (mxArray *)malloc(sizeof(mxArray));
+  a->m = m; a->n = n;
+  a->pr = (double *)calloc(m * n ? m * n : 1, sizeof(double));
+  return a;
+}
+static inline void *mxMalloc(size_t n) { return malloc(n); }
+static inline void mxFree(void *p) { free(p); }
+
+void mexFunction(int nlhs, mxArray *plhs[], int nrhs, const mxArray *prhs[]);
+#endif

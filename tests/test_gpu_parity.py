@@ -1,0 +1,148 @@
+"""-m gpu: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+
+from gp_dla_detection_b200.process_qsos import DlaContext, PackedBatch, finish_outputs, process_qsos
+from tests.helpers import assert_parity, oracle_batch, prepared_config
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_gpu(prepared, samples, k, S, lp_dla, lp_no, num_lines=3, **kw):
+    with DlaContext(k=k, num_lines=num_lines, num_samples=S, **kw) as ctx:
+        ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+        out = ctx.eval_batch(PackedBatch(prepared, k), lp_dla, lp_no)
+        out["_timing"] = ctx.timing()
+    return out
+
+
+def test_voigt_seam_matches_reference_voigt_c(oracle):
+    """dla_voigt == the voigt MEX (voigt.c verbatim where built, else the C restatement)."""
+    params, model, samples, sp, prepared = prepared_config("config1", 2, 8)
+    ref_fn = oracle.voigt_ref if oracle.load_ref() is not None else oracle.voigt_c
+    with DlaContext(k=20, num_samples=8) as ctx:
+        for p in prepared:
+            for frac, N in [(0.5, 0.0), (0.1, 1e20), (0.5, 10 ** 20.5), (0.9, 1e21), (0.3, 1e22), (0.7, 1e23)]:
+                z = p.min_z_dla + (p.max_z_dla - p.min_z_dla) * frac
+                got = ctx.voigt(p.padded_wavelengths, z, N, 3)
+                ref = ref_fn(p.padded_wavelengths, z, N, 3)
+                assert got.shape == ref.shape == (p.n_full,)
+                assert np.max(np.abs(got - ref)) <= 1e-12
+        # K2: N = 0 gives exactly 1.0 everywhere (sum of taps in tap order)
+        assert np.all(ctx.voigt(prepared[0].padded_wavelengths, 3.0, 0.0, 3) == 1.0)
+        # all 31 lines (the MEX default, voigt.c:16)
+        p = prepared[0]
+        z = p.min_z_dla + 0.4 * (p.max_z_dla - p.min_z_dla)
+        assert np.max(np.abs(ctx.voigt(p.padded_wavelengths, z, 1e21, None) - ref_fn(p.padded_wavelengths, z, 1e21, 31))) <= 1e-12
+
+
+@pytest.mark.parametrize("n,k", [(64, 1), (97, 5), (256, 20), (1217, 20), (1000, 13)])
+def test_log_mvnpdf_low_rank_seam(oracle, n, k):
+    rng = np.random.default_rng(n * 100 + k)
+    y, mu = rng.standard_normal(n), rng.standard_normal(n) * 0.1
+    M = rng.standard_normal((n, k)) * 0.5
+    d = np.exp(rng.standard_normal(n) * 0.7) * 0.05
+    with DlaContext(k=20, num_samples=8) as ctx:
+        got = ctx.log_mvnpdf_low_rank(y, mu, M, d)
+    ref = oracle.log_mvnpdf_low_rank_c(y, mu, M, d)
+    assert abs(got - ref) <= 1e-10 * abs(ref)
+    if n <= 256:
+        assert abs(got - oracle.log_mvnpdf_dense(y, mu, M, d)) <= 1e-9 * abs(ref)
+
+
+def test_tiny_config_parity(oracle):
+    params, model, samples, sp, prepared = prepared_config("tiny", 4, 64)
+    got = _run_gpu(prepared, samples, 5, 64, sp.log_priors_dla, sp.log_priors_no_dla)
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(got, ref)
+
+
+def test_config1_subset_parity(oracle):
+    """config 1 shape (n = 1217, k = 20) on a sample subset the oracle finishes in seconds."""
+    params, model, samples, sp, prepared = prepared_config("config1", 3, 700)  # S not a multiple of 64
+    got = _run_gpu(prepared, samples, 20, 700, sp.log_priors_dla, sp.log_priors_no_dla)
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    worst = assert_parity(got, ref)
+    print("config1 subset worst per-sample rel err", worst)
+
+
+@pytest.mark.parametrize("mask_gather", ["reference", "intended"])
+def test_ragged_config3_parity(oracle, mask_gather):
+    params, model, samples, sp, prepared = prepared_config("config3", 6, 192, mask_gather)
+    assert len({p.n for p in prepared}) > 1
+    got = _run_gpu(prepared, samples, 20, 192, sp.log_priors_dla, sp.log_priors_no_dla)
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(got, ref)
+
+
+def test_chunking_and_staged_api_are_bitwise_identical():
+    params, model, samples, sp, prepared = prepared_config("config3", 7, 256)
+    k, S = 20, 256
+    a = _run_gpu(prepared, samples, k, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    # a workspace that fits one quasar at a time -> 7 chunks
+    b = _run_gpu(prepared, samples, k, S, sp.log_priors_dla, sp.log_priors_no_dla, workspace_bytes=16 * 320 * 1232)
+    assert b["_timing"]["chunks"] > 1 and a["_timing"]["chunks"] == 1
+    with DlaContext(k=k, num_samples=S, store_sample_ll=False) as ctx:
+        ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+        ctx.stage(PackedBatch(prepared, k), sp.log_priors_dla, sp.log_priors_no_dla)
+        ctx.run_staged()
+        ctx.run_staged()
+        c = ctx.fetch()
+    for key in ("log_likelihoods_no_dla", "log_likelihoods_dla", "log_posteriors_dla", "model_posteriors", "map_ind"):
+        assert np.array_equal(a[key], b[key]), key
+        assert np.array_equal(a[key], c[key]), key
+    assert np.array_equal(a["sample_log_likelihoods_dla"], b["sample_log_likelihoods_dla"])
+    assert c["sample_log_likelihoods_dla"] is None
+
+
+def test_edge_semantics(oracle):
+    """-inf priors (process_qsos.m:129-132), N = 0 sample == no-DLA likelihood (K7),
+    unguarded min_z > max_z (:160-165), tiny n."""
+    params, model, samples, sp, prepared = prepared_config("config1", 2, 64)
+    off = samples.offset_samples.copy()
+    nhi = samples.nhi_samples.copy()
+    nhi[5] = 0.0
+    prepared[1].min_z_dla, prepared[1].max_z_dla = prepared[1].max_z_dla, prepared[1].min_z_dla
+    lp_dla = np.array([-np.inf, np.log(0.3)])
+    lp_no = np.array([0.0, np.log(0.7)])
+    with DlaContext(k=20, num_samples=64) as ctx:
+        ctx.set_samples(off, nhi)
+        got = ctx.eval_batch(PackedBatch(prepared, 20), lp_dla, lp_no)
+    assert got["sample_log_likelihoods_dla"][0, 5] == pytest.approx(got["log_likelihoods_no_dla"][0], rel=1e-13)
+    assert got["log_posteriors_dla"][0] == -np.inf
+    assert got["model_posteriors"][0, 0] == 1.0 and got["model_posteriors"][0, 1] == 0.0
+
+    class S_:  # same samples object shape as DLASamples
+        offset_samples, nhi_samples = off, nhi
+    ref = oracle_batch(oracle, prepared, S_, lp_dla, lp_no)
+    assert_parity(got, ref)
+
+
+def test_full_size_properties():
+    """BASELINE config-1 shape at full S = 10000: size-independent properties (K7, K10)."""
+    params, model, samples, sp, prepared = prepared_config("config1", 4, 10000)
+    S = 10000
+    got = _run_gpu(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    ll = got["sample_log_likelihoods_dla"]
+    assert np.all(np.isfinite(ll))
+    # K10 (calc_cddf.py:98, :244-246): normalised sample likelihoods sum to 1
+    norm = np.exp(ll - (got["log_likelihoods_dla"][:, None] + np.log(S))).sum(axis=1)
+    assert np.allclose(norm, 1.0, rtol=1e-10)
+    assert np.array_equal(got["map_ind"], np.argmax(ll, axis=1))
+    assert np.allclose(got["model_posteriors"].sum(axis=1), 1.0, rtol=1e-14)
+    # injected DLAs are found, clean sightlines are not
+    p_dla = 1 - got["model_posteriors"][:, 0]
+    print("p_dla", p_dla, "injected", sp.injected)
+
+
+def test_process_qsos_drop_in(oracle):
+    params, model, samples, sp, prepared = prepared_config("tiny", 4, 64)
+    out = process_qsos(sp.all_wavelengths, sp.all_flux, sp.all_noise_variance, sp.all_pixel_mask, sp.z_qsos, model,
+                       samples, sp.log_priors_dla, sp.log_priors_no_dla, params)
+    for key in ("min_z_dlas", "max_z_dlas", "log_priors_no_dla", "log_priors_dla", "log_likelihoods_no_dla",
+                "sample_log_likelihoods_dla", "log_likelihoods_dla", "log_posteriors_no_dla", "log_posteriors_dla",
+                "model_posteriors", "p_no_dlas", "p_dlas"):  # process_qsos.m:235-243
+        assert key in out
+    assert np.allclose(out["p_dlas"], 1 - out["model_posteriors"][:, 0])
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(out, ref)
