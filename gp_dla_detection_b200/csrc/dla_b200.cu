@@ -247,7 +247,9 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     const double sigma = DLA_SIGMA, s2pi = 2.50662827463100050242;
     for (int j = 0; j < DLA_MAX_LINES; ++j) {
       h.y[j] = gam[j] / sqrt(2.0) / sigma;
+      h.y2[j] = h.y[j] * h.y[j];
       h.coef[j] = lc[j] / s2pi / sigma;
+      h.cw[j] = h.coef[j] * h.y[j] * DLA_INV_SQRTPI;
       if (!(h.y[j] > DLA_FADD_YMIN && h.y[j] < DLA_FADD_YMAX)) {
         g_create_error = "dla_create: Lorentz width outside the validated Faddeeva domain";
         delete c;

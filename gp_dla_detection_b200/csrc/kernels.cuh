@@ -46,8 +46,10 @@ constexpr double LOG_2PI = 1.83787706640934534;  // log_mvnpdf_low_rank.m:7
 // y_j = gamma_j / sqrt(2) / sigma ; coef_j = leading_constants[j] / sqrt(2 pi) / sigma.
 struct LineConsts {
   double y[DLA_MAX_LINES];
-  double coef[DLA_MAX_LINES];
-  double inv_sqrt2_sigma;  // 1 / (sqrt(2) sigma)
+  double y2[DLA_MAX_LINES];    // y_j^2
+  double coef[DLA_MAX_LINES];  // multiplies Re w on the core path
+  double cw[DLA_MAX_LINES];    // coef_j * y_j / sqrt(pi): multiplies s (G - ...) on the wing path
+  double inv_sqrt2_sigma;      // 1 / (sqrt(2) sigma)
 };
 __device__ __constant__ LineConsts g_lines;
 
@@ -108,27 +110,26 @@ __global__ void build_bmat_kernel(const QuasarDesc* __restrict__ desc, int q0, c
 // Sample index S is the no-DLA pseudo-sample (a == 1, process_qsos.m:150-152); samples > S
 // are padding of the last sample block and produce zeros.
 // ----------------------------------------------------------------------------------------------
+// optical depth per unit column density of line j at wavelength lambda: lc_j * V(v; sigma, gamma_j)
+__device__ __forceinline__ double line_tau(double lambda, double mult_j, int j) {
+  const double velocity = __dsub_rn(__dmul_rn(lambda, mult_j), DLA_C_CGS);  // voigt.c:287, no FMA
+  const double x = fabs(velocity * g_lines.inv_sqrt2_sigma);
+  if (x < DLA_FADD_XNEAR) return g_lines.coef[j] * dla_re_w_near(x, g_lines.y[j], dla_wgrid);
+  return dla_re_w_wing_scaled(x * x, g_lines.cw[j], g_lines.y2[j]);
+}
+
 __device__ __forceinline__ double raw_transmission(double lambda, const double* mult, double N, int num_lines) {
-  // voigt.c:283-291
-  double total = 0.0;
-  for (int j = 0; j < num_lines; ++j) {
-    const double velocity = __dsub_rn(__dmul_rn(lambda, mult[j]), DLA_C_CGS);  // voigt.c:287, no FMA
-    const double x = velocity * g_lines.inv_sqrt2_sigma;
-    total -= g_lines.coef[j] * dla_re_w(x, g_lines.y[j], fadd_expa2n2);
-  }
-  return exp(N * total);
+  double total = 0.0;  // voigt.c:283-291
+  for (int j = 0; j < num_lines; ++j) total += line_tau(lambda, mult[j], j);
+  return exp(-N * total);
 }
 
 template <int NUM_LINES>
 __device__ __forceinline__ double raw_transmission_fixed(double lambda, const double* mult, double N) {
   double total = 0.0;
 #pragma unroll
-  for (int j = 0; j < NUM_LINES; ++j) {
-    const double velocity = __dsub_rn(__dmul_rn(lambda, mult[j]), DLA_C_CGS);
-    const double x = velocity * g_lines.inv_sqrt2_sigma;
-    total -= g_lines.coef[j] * dla_re_w(x, g_lines.y[j], fadd_expa2n2);
-  }
-  return exp(N * total);
+  for (int j = 0; j < NUM_LINES; ++j) total += line_tau(lambda, mult[j], j);
+  return exp(-N * total);
 }
 
 __global__ void __launch_bounds__(K1_THREADS, 1)
@@ -171,7 +172,7 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
 #pragma unroll
         for (int j = 0; j < 3; ++j)  // voigt.c:278-279
           mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], __dadd_rn(1.0, z)) / 1e8;
-        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission_fixed<3>(lam[i], mult, N);
+        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission_fixed<3>(__ldg(lam + i), mult, N);
       } else {
         for (int j = 0; j < num_lines; ++j)
           mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], __dadd_rn(1.0, z)) / 1e8;
@@ -180,6 +181,10 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     }
     __syncwarp();
     double q0acc = 0.0, ldacc = 0.0;
+    // sum_p log d_p is accumulated as log(prod d_p): a running product renormalised to [1,2)
+    // with the exponents summed as integers -> one log per lane per sample instead of one per pixel
+    double dprod = 1.0;
+    int esum = 0;
     for (int j0 = 0; j0 < d.npad; j0 += 32) {
       const int j = j0 + lane;
       double w = 0.0, u = 0.0;
@@ -187,18 +192,26 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
         double a = 1.0;
         if (!no_dla) {
           const double* rp = raw + pidx[j];
-          a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order, mul then add
+          a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
 #pragma unroll
-          for (int t = 0; t < 7; ++t) a = __dadd_rn(a, __dmul_rn(rp[t], dla_instrument_profile[t]));
+          for (int t = 0; t < 7; ++t) a = fma(rp[t], dla_instrument_profile[t], a);
         }
         const double a2 = a * a;
-        const double dd = om_[j] * a2 + nv_[j];   // process_qsos.m:193, :197
-        const double r = y_[j] - mu_[j] * a;      // process_qsos.m:191, log_mvnpdf_low_rank.m:11
-        const double rinv = 1.0 / dd;             // log_mvnpdf_low_rank.m:13
+        const double dd = fma(om_[j], a2, nv_[j]);   // process_qsos.m:193, :197
+        const double r = fma(-mu_[j], a, y_[j]);     // process_qsos.m:191, log_mvnpdf_low_rank.m:11
+        const double rinv = dla_fast_rcp(dd);        // log_mvnpdf_low_rank.m:13
         w = a2 * rinv;
         u = (a * r) * rinv;
-        q0acc += (r * r) * rinv;
-        ldacc += log(dd);
+        q0acc = fma(r * r, rinv, q0acc);
+        if (dd > 1e-300 && dd < 1e300) {
+          dprod *= dd;
+          const int hi = __double2hiint(dprod);
+          const int e = ((hi >> 20) & 0x7ff) - 1023;
+          esum += e;
+          dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
+        } else {
+          ldacc += log(dd);
+        }
       }
       if (j < d.npad) {
         const int64_t off = ((int64_t)(j >> 2) * TS + srow) * 4 + (j & 3);
@@ -206,6 +219,7 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
         Uq[off] = u;
       }
     }
+    ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       q0acc += __shfl_xor_sync(0xffffffffu, q0acc, o);
@@ -232,7 +246,7 @@ __global__ void voigt_single_kernel(const double* __restrict__ lambdas, int num_
   for (int i = threadIdx.x; i < num_points - 6; i += blockDim.x) {
     double a = 0.0;
 #pragma unroll
-    for (int t = 0; t < 7; ++t) a = __dadd_rn(a, __dmul_rn(raw[i + t], dla_instrument_profile[t]));
+    for (int t = 0; t < 7; ++t) a = fma(raw[i + t], dla_instrument_profile[t], a);
     profile[i] = a;
   }
 }

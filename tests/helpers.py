@@ -35,7 +35,9 @@ def assert_parity(got, ref, check_map=True):
     rel = np.abs(a - b) / np.maximum(np.abs(b), 1e-300)
     assert np.nanmax(rel) <= RTOL_SAMPLE_LL, f"per-sample ll rel err {np.nanmax(rel):.3e}"
     for key in ("log_likelihoods_no_dla", "log_likelihoods_dla", "log_posteriors_no_dla", "log_posteriors_dla"):
-        err = np.max(np.abs(got[key] - ref[key]))
+        same = got[key] == ref[key]          # covers -inf priors (process_qsos.m:129-132)
+        with np.errstate(invalid="ignore"):
+            err = np.max(np.where(same, 0.0, np.abs(got[key] - ref[key])))
         assert err <= ATOL_LOG_POST, f"{key} abs err {err:.3e}"
     assert np.max(np.abs(got["model_posteriors"] - ref["model_posteriors"])) <= 1e-6
     dec_got = got["log_posteriors_dla"] > got["log_posteriors_no_dla"]
