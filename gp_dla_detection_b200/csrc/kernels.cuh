@@ -167,16 +167,16 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
       // process_qsos.m:163-165: min + (max - min) * offset, separately rounded
       const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), offset_samples[s]));
       const double N = nhi_samples[s];
-      double mult[DLA_MAX_LINES];
+      const double opz = __dadd_rn(1.0, z);
       if (num_lines == 3) {
+        double mult3[3];  // voigt.c:278-279 (registers: every index below is static)
 #pragma unroll
-        for (int j = 0; j < 3; ++j)  // voigt.c:278-279
-          mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], __dadd_rn(1.0, z)) / 1e8;
-        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission_fixed<3>(__ldg(lam + i), mult, N);
+        for (int j = 0; j < 3; ++j) mult3[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
+        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission_fixed<3>(__ldg(lam + i), mult3, N);
       } else {
-        for (int j = 0; j < num_lines; ++j)
-          mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], __dadd_rn(1.0, z)) / 1e8;
-        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission(lam[i], mult, N, num_lines);
+        double mult[DLA_MAX_LINES];
+        for (int j = 0; j < num_lines; ++j) mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
+        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission(__ldg(lam + i), mult, N, num_lines);
       }
     }
     __syncwarp();
@@ -289,48 +289,63 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // Packed lower-triangular index, row i >= column l.
 __device__ __forceinline__ int tri(int i, int l) { return ((i * (i + 1)) >> 1) + l; }
 
-// Per-sample epilogue on one row of the accumulator tile in shared memory, executed by a
-// quad (4 consecutive lanes). row[0..210): vech(G) (B = I + G), row[VOFF..VOFF+k): v.
-// Cholesky of the bordered matrix [[B, v],[v^T, q0]]: the border row ends as t = L^-1 v and
-// the corner as q0 - t^T t = r^T K^-1 r (log_mvnpdf_low_rank.m:24-32).  Returns log p on all
-// four lanes.
-__device__ __forceinline__ double chol_logp_quad(double* row, int k, int t, double q0, double ld, int n) {
-  double logdiag = 0.0;
-  double qq = q0;
-  const int vowner = k & 3;
-  // add the identity (log_mvnpdf_low_rank.m:23)
-  for (int i = t; i < k; i += 4) row[tri(i, i)] += 1.0;
-  __syncwarp();
-  for (int j = 0; j < k; ++j) {
-    const double djj = row[tri(j, j)];
-    const double ljj = sqrt(djj);
-    const double inv = 1.0 / ljj;
-    if ((j & 3) == t) logdiag += log(ljj);
-    // scale column j below the diagonal
-    int i0 = j + 1 + ((t - (j + 1)) & 3);
-    for (int i = i0; i < k; i += 4) row[tri(i, j)] *= inv;
-    if (t == vowner) row[VOFF + j] *= inv;
-    __syncwarp();
-    // trailing update
-    for (int i = i0; i < k; i += 4) {
-      const double lij = row[tri(i, j)];
-      double* ri = row + tri(i, 0);
-      for (int l = j + 1; l <= i; ++l) ri[l] -= lij * row[tri(l, j)];
+// Per-sample epilogue, register resident.  A quad (4 consecutive lanes) owns one sample: lane t
+// of the quad holds rows i = 4r + t (r = 0..5) of the bordered 21 x 21 matrix
+//     [[ B = I + G , v ], [ v^T , q0 ]]            (rows k..19 are identity padding when k < 20)
+// in registers (all loops are fully unrolled, so every register index is static and identical
+// for the four lanes; ownership only enters through predicates).  Right-looking Cholesky: the
+// pivot and the column entries L(l,j) travel by quad shuffles.  The border row ends as
+// t = L^-1 v and the corner as q0 - t^T t = r^T K^-1 r; log|B| = sum log pivots
+// (log_mvnpdf_low_rank.m:23-32).  No shared-memory traffic after the initial load.
+// row[0..210): vech(G), row[VOFF..VOFF+k): v.  Returns log p on all four lanes.
+__device__ __forceinline__ double chol_logp_quad(const double* __restrict__ row, int k, int t, double q0, double ld,
+                                                 int n) {
+  constexpr int NB = KMAX;      // border row index (20)
+  constexpr int NR = 6;         // local rows per lane
+  double A[NR][NB + 1];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const int i = 4 * r + t;
+#pragma unroll
+    for (int l = 0; l <= NB; ++l) {
+      if (l > 4 * r + 3) continue;  // never referenced for this local row
+      double v = 0.0;
+      if (i < k) {
+        if (l <= i) v = row[tri(i, l)] + (l == i ? 1.0 : 0.0);
+      } else if (i < NB) {
+        v = (l == i) ? 1.0 : 0.0;
+      } else if (i == NB) {
+        v = (l < k) ? row[VOFF + l] : (l == NB ? q0 : 0.0);
+      }
+      A[r][l] = v;
     }
-    if (t == vowner) {
-      const double vj = row[VOFF + j];
-      for (int l = j + 1; l < k; ++l) row[VOFF + l] -= vj * row[tri(l, j)];
-      qq -= vj * vj;
-    }
-    __syncwarp();
   }
-  // combine across the quad
-  logdiag += __shfl_xor_sync(0xffffffffu, logdiag, 1);
-  logdiag += __shfl_xor_sync(0xffffffffu, logdiag, 2);
-  const int lane = threadIdx.x & 31;
-  qq = __shfl_sync(0xffffffffu, qq, (lane & ~3) | vowner);
-  // log_mvnpdf_low_rank.m:30-32
-  return -0.5 * (qq + (ld + 2.0 * logdiag) + (double)n * LOG_2PI);
+  double pprod = 1.0;  // product of the pivots this lane is responsible for (j = t mod 4): <= 5 factors
+#pragma unroll
+  for (int j = 0; j < NB; ++j) {
+    const int rj = j >> 2, tj = j & 3;
+    const double piv = __shfl_sync(0xffffffffu, A[rj][j], tj, 4);
+    const double inv = rsqrt(piv);
+    pprod *= (t == tj) ? piv : 1.0;
+#pragma unroll
+    for (int r = rj; r < NR; ++r) A[r][j] *= inv;  // entries with i <= j are never read again
+#pragma unroll
+    for (int l = j + 1; l <= NB; ++l) {
+      const int rl = l >> 2, tl = l & 3;
+      const double Llj = __shfl_sync(0xffffffffu, A[rl][j], tl, 4);
+#pragma unroll
+      for (int r = rl; r < NR; ++r) {
+        const double m = (r > rl || t >= tl) ? A[r][j] : 0.0;  // only rows i >= l
+        A[r][l] = fma(-m, Llj, A[r][l]);
+      }
+    }
+  }
+  const double qq = __shfl_sync(0xffffffffu, A[NR - 1][NB], 0, 4);  // row 20 lives on lane 0 of the quad
+  double logdet = log(pprod);
+  logdet += __shfl_xor_sync(0xffffffffu, logdet, 1);
+  logdet += __shfl_xor_sync(0xffffffffu, logdet, 2);
+  // log_mvnpdf_low_rank.m:30-32 (2 sum log diag(L) = sum log pivots)
+  return -0.5 * (qq + (ld + logdet) + (double)n * LOG_2PI);
 }
 
 __global__ void __launch_bounds__(K2_THREADS, 1)
