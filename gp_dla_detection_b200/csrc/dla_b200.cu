@@ -244,19 +244,37 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     CREATE_TRY(cudaMemcpyFromSymbol(gam, dla_gammas, sizeof gam));
     CREATE_TRY(cudaMemcpyFromSymbol(lc, dla_leading_constants, sizeof lc));
     dla::LineConsts h;
+    memset(&h, 0, sizeof h);
     const double sigma = DLA_SIGMA, s2pi = 2.50662827463100050242;
+    const double T = 2.0 * sigma * sigma;
     for (int j = 0; j < DLA_MAX_LINES; ++j) {
       h.y[j] = gam[j] / sqrt(2.0) / sigma;
-      h.y2[j] = h.y[j] * h.y[j];
       h.coef[j] = lc[j] / s2pi / sigma;
-      h.cw[j] = h.coef[j] * h.y[j] * DLA_INV_SQRTPI;
+      h.cwT[j] = h.coef[j] * h.y[j] * DLA_INV_SQRTPI * T;
+      h.y2T[j] = h.y[j] * h.y[j] * T;
       if (!(h.y[j] > DLA_FADD_YMIN && h.y[j] < DLA_FADD_YMAX)) {
         g_create_error = "dla_create: Lorentz width outside the validated Faddeeva domain";
         delete c;
         return DLA_ERR_BAD_ARG;
       }
     }
+    {
+      const double g[7] = {1.0, 1.5, 3.75, 13.125, 59.0625, 324.84375, 2111.484375};  // (2n+1)!!/2^n
+      double tp = 1.0;
+      for (int n = 0; n < 7; ++n) { h.gq[n] = g[n] * tp; tp *= T; }
+    }
+    h.fiveT = 5.0 * T;
+    h.vnear2 = (DLA_FADD_XNEAR * sqrt(2.0) * sigma) * (DLA_FADD_XNEAR * sqrt(2.0) * sigma);
     h.inv_sqrt2_sigma = 1.0 / (sqrt(2.0) * sigma);
+    h.c_cgs = DLA_C_CGS;
+    h.l2e = 1.4426950408889634074;
+    h.magic = 6755399441055744.0;  // 1.5 * 2^52: adding it rounds to the nearest integer
+    h.nln2hi = -6.93147180369123816490e-01;
+    h.nln2lo = -1.90821492927058770002e-10;
+    {
+      double f = 1.0;
+      for (int n = 0; n < 14; ++n) { if (n > 0) f *= n; h.ec[n] = 1.0 / f; }
+    }
     CREATE_TRY(cudaMemcpyToSymbol(dla::g_lines, &h, sizeof h));
   }
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -42,14 +42,24 @@ constexpr int LDC = NCOL + 2;   // epilogue row stride (doubles)
 constexpr int K1_THREADS = 512;
 constexpr double LOG_2PI = 1.83787706640934534;  // log_mvnpdf_low_rank.m:7
 
-// Per-line constants prepared on the host exactly as libcerf/voigt.c would:
-// y_j = gamma_j / sqrt(2) / sigma ; coef_j = leading_constants[j] / sqrt(2 pi) / sigma.
+// Constants of the Voigt kernel, prepared once on the host (dla_create) and read as
+// constant-bank operands (no immediate materialisation in the inner loops).
+// Per line, as libcerf/voigt.c would: y_j = gamma_j/sqrt(2)/sigma, coef_j = lc_j/sqrt(2 pi)/sigma.
+// The wing series is evaluated in sp = 1/velocity^2 directly: with T = 2 sigma^2 (s = T sp),
+//   lc_j V = (cwT_j sp) [ sum_n gq_n sp^n - (y2T_j sp)(1 + fiveT sp) ],  gq_n = (2n+1)!!/2^n T^n.
 struct LineConsts {
   double y[DLA_MAX_LINES];
-  double y2[DLA_MAX_LINES];    // y_j^2
   double coef[DLA_MAX_LINES];  // multiplies Re w on the core path
-  double cw[DLA_MAX_LINES];    // coef_j * y_j / sqrt(pi): multiplies s (G - ...) on the wing path
+  double cwT[DLA_MAX_LINES];   // coef_j y_j / sqrt(pi) * T
+  double y2T[DLA_MAX_LINES];   // y_j^2 * T
+  double gq[7];
+  double fiveT;
+  double vnear2;               // (16 sqrt(2) sigma)^2: below it the core path is used
   double inv_sqrt2_sigma;      // 1 / (sqrt(2) sigma)
+  double c_cgs;
+  // exp(t), t <= 0: t = k ln2 + r, Taylor degree 13 in r
+  double l2e, magic, nln2hi, nln2lo;
+  double ec[14];
 };
 __device__ __constant__ LineConsts g_lines;
 
@@ -110,18 +120,44 @@ __global__ void build_bmat_kernel(const QuasarDesc* __restrict__ desc, int q0, c
 // Sample index S is the no-DLA pseudo-sample (a == 1, process_qsos.m:150-152); samples > S
 // are padding of the last sample block and produce zeros.
 // ----------------------------------------------------------------------------------------------
+// exp(t) for t <= 0 (NaN propagates): k = rint(t log2 e), r = t - k ln2 (hi/lo split), Taylor
+// degree 13 (|r| <= 0.347: truncation 4e-18), result scaled by 2^k in two exact steps so that
+// results below 2^-1022 denormalise / underflow to 0 as libm's exp does.  All coefficients are
+// constant-bank operands.
+__device__ __forceinline__ double exp_nonpos(double t) {
+  t = (t < -1500.0) ? -1500.0 : t;
+  const double kd = fma(t, g_lines.l2e, g_lines.magic);
+  const int ki = __double2loint(kd);
+  const double kf = kd - g_lines.magic;
+  double r = fma(kf, g_lines.nln2hi, t);
+  r = fma(kf, g_lines.nln2lo, r);
+  double p = g_lines.ec[13];
+#pragma unroll
+  for (int n = 12; n >= 0; --n) p = fma(p, r, g_lines.ec[n]);
+  const int k1 = ki >> 1, k2 = ki - k1;
+  const double s1 = __hiloint2double((k1 + 1023) << 20, 0);
+  const double s2 = __hiloint2double((k2 + 1023) << 20, 0);
+  return (p * s1) * s2;
+}
+
 // optical depth per unit column density of line j at wavelength lambda: lc_j * V(v; sigma, gamma_j)
 __device__ __forceinline__ double line_tau(double lambda, double mult_j, int j) {
-  const double velocity = __dsub_rn(__dmul_rn(lambda, mult_j), DLA_C_CGS);  // voigt.c:287, no FMA
-  const double x = fabs(velocity * g_lines.inv_sqrt2_sigma);
-  if (x < DLA_FADD_XNEAR) return g_lines.coef[j] * dla_re_w_near(x, g_lines.y[j], dla_wgrid);
-  return dla_re_w_wing_scaled(x * x, g_lines.cw[j], g_lines.y2[j]);
+  const double velocity = __dsub_rn(__dmul_rn(lambda, mult_j), g_lines.c_cgs);  // voigt.c:287, no FMA
+  const double v2 = velocity * velocity;
+  if (v2 < g_lines.vnear2)  // |x| < 16: line core (rare)
+    return g_lines.coef[j] * dla_re_w_near(fabs(velocity * g_lines.inv_sqrt2_sigma), g_lines.y[j], dla_wgrid);
+  const double sp = dla_fast_rcp(v2);
+  double G = g_lines.gq[6];
+#pragma unroll
+  for (int n = 5; n >= 0; --n) G = fma(G, sp, g_lines.gq[n]);
+  const double corr = (g_lines.y2T[j] * sp) * fma(g_lines.fiveT, sp, 1.0);
+  return (g_lines.cwT[j] * sp) * (G - corr);
 }
 
 __device__ __forceinline__ double raw_transmission(double lambda, const double* mult, double N, int num_lines) {
   double total = 0.0;  // voigt.c:283-291
   for (int j = 0; j < num_lines; ++j) total += line_tau(lambda, mult[j], j);
-  return exp(-N * total);
+  return exp_nonpos(-N * total);
 }
 
 template <int NUM_LINES>
@@ -129,7 +165,7 @@ __device__ __forceinline__ double raw_transmission_fixed(double lambda, const do
   double total = 0.0;
 #pragma unroll
   for (int j = 0; j < NUM_LINES; ++j) total += line_tau(lambda, mult[j], j);
-  return exp(-N * total);
+  return exp_nonpos(-N * total);
 }
 
 __global__ void __launch_bounds__(K1_THREADS, 1)
@@ -185,39 +221,39 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     // with the exponents summed as integers -> one log per lane per sample instead of one per pixel
     double dprod = 1.0;
     int esum = 0;
-    for (int j0 = 0; j0 < d.npad; j0 += 32) {
-      const int j = j0 + lane;
+    // this lane's first element of the [pixel/4][64][4] tile layout; +32 pixels = +8 pixel groups
+    double* wp = Wq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
+    double* up = Uq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
+    for (int j = lane; j < d.npad; j += 32, wp += 8 * TS * 4, up += 8 * TS * 4) {
       double w = 0.0, u = 0.0;
       if (j < d.n && !phantom) {
         double a = 1.0;
         if (!no_dla) {
-          const double* rp = raw + pidx[j];
+          const double* rp = raw + __ldg(pidx + j);
           a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
 #pragma unroll
           for (int t = 0; t < 7; ++t) a = fma(rp[t], dla_instrument_profile[t], a);
         }
         const double a2 = a * a;
-        const double dd = fma(om_[j], a2, nv_[j]);   // process_qsos.m:193, :197
-        const double r = fma(-mu_[j], a, y_[j]);     // process_qsos.m:191, log_mvnpdf_low_rank.m:11
-        const double rinv = dla_fast_rcp(dd);        // log_mvnpdf_low_rank.m:13
+        const double dd = fma(__ldg(om_ + j), a2, __ldg(nv_ + j));  // process_qsos.m:193, :197
+        const double r = fma(-__ldg(mu_ + j), a, __ldg(y_ + j));    // process_qsos.m:191, log_mvnpdf_low_rank.m:11
+        const double rinv = dla_fast_rcp(dd);                       // log_mvnpdf_low_rank.m:13
         w = a2 * rinv;
         u = (a * r) * rinv;
         q0acc = fma(r * r, rinv, q0acc);
-        if (dd > 1e-300 && dd < 1e300) {
+        // positive, normal and < 2^1022 (one integer compare on the high word)
+        if ((unsigned)(__double2hiint(dd) - 0x00100000) < 0x7fc00000u) {
           dprod *= dd;
           const int hi = __double2hiint(dprod);
-          const int e = ((hi >> 20) & 0x7ff) - 1023;
+          const int e = (hi >> 20) - 1023;
           esum += e;
           dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
         } else {
           ldacc += log(dd);
         }
       }
-      if (j < d.npad) {
-        const int64_t off = ((int64_t)(j >> 2) * TS + srow) * 4 + (j & 3);
-        Wq[off] = w;
-        Uq[off] = u;
-      }
+      *wp = w;
+      *up = u;
     }
     ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
 #pragma unroll
@@ -227,7 +263,7 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     }
     if (lane == 0) {
       auxq[s] = q0acc;
-      auxq[S_pad + s] = ldacc;
+      auxq[S_pad + s] = phantom ? 0.0 : ldacc;
     }
     __syncwarp();
   }
