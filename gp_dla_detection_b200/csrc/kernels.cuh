@@ -125,7 +125,7 @@ __global__ void build_bmat_kernel(const QuasarDesc* __restrict__ desc, int q0, c
 // results below 2^-1022 denormalise / underflow to 0 as libm's exp does.  All coefficients are
 // constant-bank operands.
 __device__ __forceinline__ double exp_nonpos(double t) {
-  t = (t < -1500.0) ? -1500.0 : t;
+  t = (t < -1400.0) ? -1400.0 : t;  // exp underflows to 0 below -745.2; keeps 2^(k/2) representable
   const double kd = fma(t, g_lines.l2e, g_lines.magic);
   const int ki = __double2loint(kd);
   const double kf = kd - g_lines.magic;
