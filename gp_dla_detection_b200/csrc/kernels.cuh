@@ -168,6 +168,46 @@ __device__ __forceinline__ double raw_transmission_fixed(double lambda, const do
   return exp_nonpos(-N * total);
 }
 
+__device__ __noinline__ double line_tau_slow(double lambda, double mult_j, int j) { return line_tau(lambda, mult_j, j); }
+
+// NPIX pixels x NUM_LINES lines evaluated together on the branch-free wing formula (independent
+// FMA chains interleave and hide the DFMA latency); the rare pixels with a line core in range
+// (|x| < 16 for some line) are then redone on the exact two-regime path.
+template <int NUM_LINES, int NPIX>
+__device__ __forceinline__ void raw_transmission_multi(const double (&lambda)[NPIX], const double* mult, double N,
+                                                       double (&out)[NPIX]) {
+  double total[NPIX];
+  bool near_any = false;
+#pragma unroll
+  for (int p = 0; p < NPIX; ++p) total[p] = 0.0;
+#pragma unroll
+  for (int j = 0; j < NUM_LINES; ++j) {
+#pragma unroll
+    for (int p = 0; p < NPIX; ++p) {
+      const double velocity = __dsub_rn(__dmul_rn(lambda[p], mult[j]), g_lines.c_cgs);  // voigt.c:287
+      const double v2 = velocity * velocity;
+      near_any |= (v2 < g_lines.vnear2);
+      const double sp = dla_fast_rcp(v2);
+      double G = g_lines.gq[6];
+#pragma unroll
+      for (int n = 5; n >= 0; --n) G = fma(G, sp, g_lines.gq[n]);
+      const double corr = (g_lines.y2T[j] * sp) * fma(g_lines.fiveT, sp, 1.0);
+      total[p] = fma(g_lines.cwT[j] * sp, G - corr, total[p]);
+    }
+  }
+  if (near_any) {
+#pragma unroll
+    for (int p = 0; p < NPIX; ++p) {
+      double t = 0.0;
+#pragma unroll
+      for (int j = 0; j < NUM_LINES; ++j) t += line_tau_slow(lambda[p], mult[j], j);
+      total[p] = t;
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < NPIX; ++p) out[p] = exp_nonpos(-N * total[p]);
+}
+
 __global__ void __launch_bounds__(K1_THREADS, 1)
 voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
                      const double* __restrict__ offset_samples, const double* __restrict__ nhi_samples,
@@ -208,7 +248,14 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
         double mult3[3];  // voigt.c:278-279 (registers: every index below is static)
 #pragma unroll
         for (int j = 0; j < 3; ++j) mult3[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
-        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission_fixed<3>(__ldg(lam + i), mult3, N);
+        for (int i = lane; i < d.P; i += 64) {
+          const bool has1 = (i + 32 < d.P);
+          const double l2[2] = {__ldg(lam + i), __ldg(lam + (has1 ? i + 32 : i))};
+          double r2[2];
+          raw_transmission_multi<3, 2>(l2, mult3, N, r2);
+          raw[i] = r2[0];
+          if (has1) raw[i + 32] = r2[1];
+        }
       } else {
         double mult[DLA_MAX_LINES];
         for (int j = 0; j < num_lines; ++j) mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
@@ -224,36 +271,56 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     // this lane's first element of the [pixel/4][64][4] tile layout; +32 pixels = +8 pixel groups
     double* wp = Wq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
     double* up = Uq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
-    for (int j = lane; j < d.npad; j += 32, wp += 8 * TS * 4, up += 8 * TS * 4) {
-      double w = 0.0, u = 0.0;
-      if (j < d.n && !phantom) {
-        double a = 1.0;
-        if (!no_dla) {
-          const double* rp = raw + __ldg(pidx + j);
-          a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
+    // two pixels per lane per iteration (j and j+32): independent chains, loads issued up front
+    for (int j = lane; j < d.npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4) {
+      double w[2] = {0.0, 0.0}, u[2] = {0.0, 0.0}, dd[2] = {1.0, 1.0};
+      bool live[2], okd[2];
+      double om2[2], nv2[2], mu2[2], y2v[2], a[2];
+      int pi2[2];
 #pragma unroll
-          for (int t = 0; t < 7; ++t) a = fma(rp[t], dla_instrument_profile[t], a);
-        }
-        const double a2 = a * a;
-        const double dd = fma(__ldg(om_ + j), a2, __ldg(nv_ + j));  // process_qsos.m:193, :197
-        const double r = fma(-__ldg(mu_ + j), a, __ldg(y_ + j));    // process_qsos.m:191, log_mvnpdf_low_rank.m:11
-        const double rinv = dla_fast_rcp(dd);                       // log_mvnpdf_low_rank.m:13
-        w = a2 * rinv;
-        u = (a * r) * rinv;
-        q0acc = fma(r * r, rinv, q0acc);
-        // positive, normal and < 2^1022 (one integer compare on the high word)
-        if ((unsigned)(__double2hiint(dd) - 0x00100000) < 0x7fc00000u) {
-          dprod *= dd;
-          const int hi = __double2hiint(dprod);
-          const int e = (hi >> 20) - 1023;
-          esum += e;
-          dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
-        } else {
-          ldacc += log(dd);
+      for (int h = 0; h < 2; ++h) {
+        const int jj = j + 32 * h;
+        live[h] = (jj < d.n) && !phantom;
+        const int jc = live[h] ? jj : 0;
+        pi2[h] = no_dla ? 0 : __ldg(pidx + jc);
+        om2[h] = __ldg(om_ + jc); nv2[h] = __ldg(nv_ + jc); mu2[h] = __ldg(mu_ + jc); y2v[h] = __ldg(y_ + jc);
+      }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        a[h] = 1.0;
+        if (!no_dla) {  // warp-uniform
+          const double* rp = raw + pi2[h];
+          double acc = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
+#pragma unroll
+          for (int t = 0; t < 7; ++t) acc = fma(rp[t], dla_instrument_profile[t], acc);
+          a[h] = acc;
         }
       }
-      *wp = w;
-      *up = u;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const double a2 = a[h] * a[h];
+        const double d_ = fma(om2[h], a2, nv2[h]);    // process_qsos.m:193, :197
+        const double r = fma(-mu2[h], a[h], y2v[h]);  // process_qsos.m:191, log_mvnpdf_low_rank.m:11
+        const double rinv = dla_fast_rcp(d_);         // log_mvnpdf_low_rank.m:13
+        const double wv = a2 * rinv, uv = (a[h] * r) * rinv, qv = (r * r) * rinv;
+        w[h] = live[h] ? wv : 0.0;
+        u[h] = live[h] ? uv : 0.0;
+        q0acc += live[h] ? qv : 0.0;
+        // positive, normal and < 2^1022 (one integer compare on the high word)
+        okd[h] = (unsigned)(__double2hiint(d_) - 0x00100000) < 0x7fc00000u;
+        dd[h] = d_;
+        dprod *= (live[h] && okd[h]) ? d_ : 1.0;
+        const int hi = __double2hiint(dprod);
+        const int e = (hi >> 20) - 1023;
+        esum += e;
+        dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
+      }
+      if ((live[0] && !okd[0]) || (live[1] && !okd[1])) {  // rare: zero / denormal / huge / NaN d
+        if (live[0] && !okd[0]) ldacc += log(dd[0]);
+        if (live[1] && !okd[1]) ldacc += log(dd[1]);
+      }
+      wp[0] = w[0]; up[0] = u[0];
+      if (j + 32 < d.npad) { wp[8 * TS * 4] = w[1]; up[8 * TS * 4] = u[1]; }
     }
     ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
 #pragma unroll
