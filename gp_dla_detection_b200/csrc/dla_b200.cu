@@ -100,7 +100,7 @@ static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * 
 // chunk execution
 // ------------------------------------------------------------------------------------------
 static int k1_warps_for(int raw_stride) {
-  const size_t budget = 200 * 1024;
+  const size_t budget = 200 * 1024 - 256;
   int w = (int)(budget / ((size_t)raw_stride * 8));
   if (w > dla::K1_THREADS / 32) w = dla::K1_THREADS / 32;
   return w;
@@ -127,7 +127,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     const int raw_stride = (int)round_up(ch.max_P, 2);
     const int warps = k1_warps_for(raw_stride);
     if (warps < 1) BAD_ARG(c, "a quasar has too many padded pixels for the Voigt kernel's shared-memory row");
-    const size_t smem = (size_t)warps * raw_stride * 8;
+    const size_t smem = (size_t)warps * raw_stride * 8 + 32 * 8;
     dla::voigt_weights_kernel<<<(unsigned)((int64_t)ch.nq * nsb), warps * 32, smem, st>>>(
         in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pidx, in.flux, in.mu, in.om, in.nv, W, U, aux,
         num_lines, raw_stride);
@@ -267,13 +267,26 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     h.vnear2 = (DLA_FADD_XNEAR * sqrt(2.0) * sigma) * (DLA_FADD_XNEAR * sqrt(2.0) * sigma);
     h.inv_sqrt2_sigma = 1.0 / (sqrt(2.0) * sigma);
     h.c_cgs = DLA_C_CGS;
-    h.l2e = 1.4426950408889634074;
-    h.magic = 6755399441055744.0;  // 1.5 * 2^52: adding it rounds to the nearest integer
-    h.nln2hi = -6.93147180369123816490e-01;
-    h.nln2lo = -1.90821492927058770002e-10;
+    h.k32 = 32.0 * 1.4426950408889634074;  // 32 / ln 2
+    h.magic = 6755399441055744.0;           // 1.5 * 2^52: adding it rounds to the nearest integer
+    h.nln2hi32 = -6.93147180369123816490e-01 / 32.0;  // exact scalings of the hi/lo split of ln 2
+    h.nln2lo32 = -1.90821492927058770002e-10 / 32.0;
     {
       double f = 1.0;
-      for (int n = 0; n < 14; ++n) { if (n > 0) f *= n; h.ec[n] = 1.0 / f; }
+      for (int n = 0; n < 7; ++n) { if (n > 0) f *= n; h.ec[n] = 1.0 / f; }
+      for (int i = 0; i < 32; ++i) h.etab[i] = exp2(i / 32.0);
+    }
+    {
+      auto hi_of = [&](double xthr) {
+        const double v = xthr * sqrt(2.0) * sigma;
+        const double v2 = v * v;
+        long long bits;
+        memcpy(&bits, &v2, 8);
+        return (int)(bits >> 32) + 1;  // strictly above the threshold: the series is only used beyond it
+      };
+      h.hi_near = hi_of(DLA_FADD_XNEAR);
+      h.hi_64 = hi_of(64.0);
+      h.hi_256 = hi_of(256.0);
     }
     CREATE_TRY(cudaMemcpyToSymbol(dla::g_lines, &h, sizeof h));
   }

@@ -57,9 +57,12 @@ struct LineConsts {
   double vnear2;               // (16 sqrt(2) sigma)^2: below it the core path is used
   double inv_sqrt2_sigma;      // 1 / (sqrt(2) sigma)
   double c_cgs;
-  // exp(t), t <= 0: t = k ln2 + r, Taylor degree 13 in r
-  double l2e, magic, nln2hi, nln2lo;
-  double ec[14];
+  // exp(t), t <= 0: t = (32 m + i) ln2/32 + r, |r| <= ln2/64: 2^m * etab[i] * Taylor_6(r)
+  double k32, magic, nln2hi32, nln2lo32;
+  double ec[7];
+  double etab[32];             // 2^(i/32)
+  // high 32 bits of the velocity^2 thresholds for |x| < 16 (core), < 64, < 256 (series length)
+  int hi_near, hi_64, hi_256, pad_;
 };
 __device__ __constant__ LineConsts g_lines;
 
@@ -120,23 +123,24 @@ __global__ void build_bmat_kernel(const QuasarDesc* __restrict__ desc, int q0, c
 // Sample index S is the no-DLA pseudo-sample (a == 1, process_qsos.m:150-152); samples > S
 // are padding of the last sample block and produce zeros.
 // ----------------------------------------------------------------------------------------------
-// exp(t) for t <= 0 (NaN propagates): k = rint(t log2 e), r = t - k ln2 (hi/lo split), Taylor
-// degree 13 (|r| <= 0.347: truncation 4e-18), result scaled by 2^k in two exact steps so that
-// results below 2^-1022 denormalise / underflow to 0 as libm's exp does.  All coefficients are
-// constant-bank operands.
-__device__ __forceinline__ double exp_nonpos(double t) {
-  t = (t < -1400.0) ? -1400.0 : t;  // exp underflows to 0 below -745.2; keeps 2^(k/2) representable
-  const double kd = fma(t, g_lines.l2e, g_lines.magic);
+// exp(t) for t <= 0 (NaN propagates): t = (32 m + i) ln2/32 + r with |r| <= ln2/64, so
+// exp(t) = 2^m * 2^(i/32) * exp(r); exp(r) by Taylor degree 6 (truncation 3e-18), 2^(i/32) from a
+// 32-entry shared-memory table, 2^m applied in two exact steps so that results below 2^-1022
+// denormalise / underflow to 0 as libm's exp does.  13 FP64 instructions.
+__device__ __forceinline__ double exp_nonpos(double t, const double* __restrict__ etab_s) {
+  t = (t < -1400.0) ? -1400.0 : t;  // exp underflows to 0 below -745.2; keeps 2^(m/2) representable
+  const double kd = fma(t, g_lines.k32, g_lines.magic);
   const int ki = __double2loint(kd);
   const double kf = kd - g_lines.magic;
-  double r = fma(kf, g_lines.nln2hi, t);
-  r = fma(kf, g_lines.nln2lo, r);
-  double p = g_lines.ec[13];
+  double r = fma(kf, g_lines.nln2hi32, t);
+  r = fma(kf, g_lines.nln2lo32, r);
+  double p = g_lines.ec[6];
 #pragma unroll
-  for (int n = 12; n >= 0; --n) p = fma(p, r, g_lines.ec[n]);
-  const int k1 = ki >> 1, k2 = ki - k1;
-  const double s1 = __hiloint2double((k1 + 1023) << 20, 0);
-  const double s2 = __hiloint2double((k2 + 1023) << 20, 0);
+  for (int n = 5; n >= 0; --n) p = fma(p, r, g_lines.ec[n]);
+  p *= etab_s[ki & 31];
+  const int m = ki >> 5, m1 = m >> 1, m2 = m - m1;
+  const double s1 = __hiloint2double((m1 + 1023) << 20, 0);
+  const double s2 = __hiloint2double((m2 + 1023) << 20, 0);
   return (p * s1) * s2;
 }
 
@@ -144,7 +148,7 @@ __device__ __forceinline__ double exp_nonpos(double t) {
 __device__ __forceinline__ double line_tau(double lambda, double mult_j, int j) {
   const double velocity = __dsub_rn(__dmul_rn(lambda, mult_j), g_lines.c_cgs);  // voigt.c:287, no FMA
   const double v2 = velocity * velocity;
-  if (v2 < g_lines.vnear2)  // |x| < 16: line core (rare)
+  if (__double2hiint(v2) < g_lines.hi_near)  // |x| < 16: line core (rare)
     return g_lines.coef[j] * dla_re_w_near(fabs(velocity * g_lines.inv_sqrt2_sigma), g_lines.y[j], dla_wgrid);
   const double sp = dla_fast_rcp(v2);
   double G = g_lines.gq[6];
@@ -154,58 +158,84 @@ __device__ __forceinline__ double line_tau(double lambda, double mult_j, int j) 
   return (g_lines.cwT[j] * sp) * (G - corr);
 }
 
-__device__ __forceinline__ double raw_transmission(double lambda, const double* mult, double N, int num_lines) {
+__device__ __forceinline__ double raw_transmission(double lambda, const double* mult, double N, int num_lines,
+                                                   const double* etab_s) {
   double total = 0.0;  // voigt.c:283-291
   for (int j = 0; j < num_lines; ++j) total += line_tau(lambda, mult[j], j);
-  return exp_nonpos(-N * total);
-}
-
-template <int NUM_LINES>
-__device__ __forceinline__ double raw_transmission_fixed(double lambda, const double* mult, double N) {
-  double total = 0.0;
-#pragma unroll
-  for (int j = 0; j < NUM_LINES; ++j) total += line_tau(lambda, mult[j], j);
-  return exp_nonpos(-N * total);
+  return exp_nonpos(-N * total, etab_s);
 }
 
 __device__ __noinline__ double line_tau_slow(double lambda, double mult_j, int j) { return line_tau(lambda, mult_j, j); }
 
-// NPIX pixels x NUM_LINES lines evaluated together on the branch-free wing formula (independent
-// FMA chains interleave and hide the DFMA latency); the rare pixels with a line core in range
-// (|x| < 16 for some line) are then redone on the exact two-regime path.
-template <int NUM_LINES, int NPIX>
-__device__ __forceinline__ void raw_transmission_multi(const double (&lambda)[NPIX], const double* mult, double N,
-                                                       double (&out)[NPIX]) {
+// One line's wing contribution with an NT-term series (NT = 7: |x| >= 16; 4: >= 64; 3: >= 256).
+// The O(y^3) correction keeps its (1 + 5 s) factor only where it matters (NT = 7).
+template <int NT>
+__device__ __forceinline__ double wing_term(double sp, int j, double total) {
+  double G = g_lines.gq[NT - 1];
+#pragma unroll
+  for (int n = NT - 2; n >= 0; --n) G = fma(G, sp, g_lines.gq[n]);
+  if (NT == 7) G -= (g_lines.y2T[j] * sp) * fma(g_lines.fiveT, sp, 1.0);
+  else G = fma(-g_lines.y2T[j], sp, G);
+  return fma(g_lines.cwT[j] * sp, G, total);
+}
+
+// Three lines x NPIX pixels evaluated together, branch-free (independent FMA chains interleave
+// and hide the DFMA latency).  The three reciprocals 1/v_j^2 of a pixel share one reciprocal of
+// the product.  The series length is chosen per warp iteration from the smallest |x| in the warp
+// (one integer warp reduction); pixels with a line core in range (|x| < 16 for some line) are then
+// redone on the exact two-regime path.
+template <int NPIX>
+__device__ __forceinline__ void raw_transmission3(const double (&lambda)[NPIX], const double (&mult)[3], double N,
+                                                  const double* etab_s, double (&out)[NPIX]) {
+  double sp[NPIX][3];
+  int minhi = 0x7fffffff;
+#pragma unroll
+  for (int p = 0; p < NPIX; ++p) {
+    double v2[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double velocity = __dsub_rn(__dmul_rn(lambda[p], mult[j]), g_lines.c_cgs);  // voigt.c:287
+      v2[j] = velocity * velocity;
+      minhi = min(minhi, __double2hiint(v2[j]));
+    }
+    const double p01 = v2[0] * v2[1];
+    const double rr = dla_fast_rcp(p01 * v2[2]);
+    const double r01 = rr * v2[2];  // 1/(v0 v1)
+    sp[p][2] = rr * p01;
+    sp[p][0] = r01 * v2[1];
+    sp[p][1] = r01 * v2[0];
+  }
+  const int wmin = __reduce_min_sync(0xffffffffu, minhi);
   double total[NPIX];
-  bool near_any = false;
 #pragma unroll
   for (int p = 0; p < NPIX; ++p) total[p] = 0.0;
+  if (wmin >= g_lines.hi_256) {
 #pragma unroll
-  for (int j = 0; j < NUM_LINES; ++j) {
+    for (int j = 0; j < 3; ++j)
 #pragma unroll
-    for (int p = 0; p < NPIX; ++p) {
-      const double velocity = __dsub_rn(__dmul_rn(lambda[p], mult[j]), g_lines.c_cgs);  // voigt.c:287
-      const double v2 = velocity * velocity;
-      near_any |= (v2 < g_lines.vnear2);
-      const double sp = dla_fast_rcp(v2);
-      double G = g_lines.gq[6];
+      for (int p = 0; p < NPIX; ++p) total[p] = wing_term<3>(sp[p][j], j, total[p]);
+  } else if (wmin >= g_lines.hi_64) {
 #pragma unroll
-      for (int n = 5; n >= 0; --n) G = fma(G, sp, g_lines.gq[n]);
-      const double corr = (g_lines.y2T[j] * sp) * fma(g_lines.fiveT, sp, 1.0);
-      total[p] = fma(g_lines.cwT[j] * sp, G - corr, total[p]);
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int p = 0; p < NPIX; ++p) total[p] = wing_term<4>(sp[p][j], j, total[p]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int p = 0; p < NPIX; ++p) total[p] = wing_term<7>(sp[p][j], j, total[p]);
+    if (minhi < g_lines.hi_near) {  // rare, divergent: a line core within this lane's pixels
+#pragma unroll
+      for (int p = 0; p < NPIX; ++p) {
+        double t = 0.0;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) t += line_tau_slow(lambda[p], mult[j], j);
+        total[p] = t;
+      }
     }
   }
-  if (near_any) {
 #pragma unroll
-    for (int p = 0; p < NPIX; ++p) {
-      double t = 0.0;
-#pragma unroll
-      for (int j = 0; j < NUM_LINES; ++j) t += line_tau_slow(lambda[p], mult[j], j);
-      total[p] = t;
-    }
-  }
-#pragma unroll
-  for (int p = 0; p < NPIX; ++p) out[p] = exp_nonpos(-N * total[p]);
+  for (int p = 0; p < NPIX; ++p) out[p] = exp_nonpos(-N * total[p], etab_s);
 }
 
 __global__ void __launch_bounds__(K1_THREADS, 1)
@@ -221,7 +251,10 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
   const QuasarDesc d = desc[q0 + ql];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nwarps = blockDim.x >> 5;
-  double* raw = k1_smem + (size_t)warp * raw_stride;
+  double* etab_s = k1_smem;  // 2^(i/32), i < 32
+  if (threadIdx.x < 32) etab_s[threadIdx.x] = g_lines.etab[threadIdx.x];
+  __syncthreads();
+  double* raw = k1_smem + 32 + (size_t)warp * raw_stride;
 
   const double* lam = padded_wavelengths + d.pad_off;
   const int32_t* pidx = profile_index + d.pix_off;
@@ -248,18 +281,18 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
         double mult3[3];  // voigt.c:278-279 (registers: every index below is static)
 #pragma unroll
         for (int j = 0; j < 3; ++j) mult3[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
-        for (int i = lane; i < d.P; i += 64) {
-          const bool has1 = (i + 32 < d.P);
-          const double l2[2] = {__ldg(lam + i), __ldg(lam + (has1 ? i + 32 : i))};
+        for (int i0 = 0; i0 < d.P; i0 += 64) {  // warp-uniform trip count (warp reduction inside)
+          const int ia = i0 + lane, ib = ia + 32;
+          const double l2[2] = {__ldg(lam + min(ia, d.P - 1)), __ldg(lam + min(ib, d.P - 1))};
           double r2[2];
-          raw_transmission_multi<3, 2>(l2, mult3, N, r2);
-          raw[i] = r2[0];
-          if (has1) raw[i + 32] = r2[1];
+          raw_transmission3<2>(l2, mult3, N, etab_s, r2);
+          if (ia < d.P) raw[ia] = r2[0];
+          if (ib < d.P) raw[ib] = r2[1];
         }
       } else {
         double mult[DLA_MAX_LINES];
         for (int j = 0; j < num_lines; ++j) mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
-        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission(__ldg(lam + i), mult, N, num_lines);
+        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission(__ldg(lam + i), mult, N, num_lines, etab_s);
       }
     }
     __syncwarp();
@@ -340,11 +373,13 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
 __global__ void voigt_single_kernel(const double* __restrict__ lambdas, int num_points, double z, double N,
                                     int num_lines, double* __restrict__ raw, double* __restrict__ profile) {
   __shared__ double mult[DLA_MAX_LINES];
+  __shared__ double etab_s[32];
+  if (threadIdx.x < 32) etab_s[threadIdx.x] = g_lines.etab[threadIdx.x];
   if (threadIdx.x < num_lines)
     mult[threadIdx.x] =
         DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[threadIdx.x], __dadd_rn(1.0, z)) / 1e8;
   __syncthreads();
-  for (int i = threadIdx.x; i < num_points; i += blockDim.x) raw[i] = raw_transmission(lambdas[i], mult, N, num_lines);
+  for (int i = threadIdx.x; i < num_points; i += blockDim.x) raw[i] = raw_transmission(lambdas[i], mult, N, num_lines, etab_s);
   __syncthreads();
   for (int i = threadIdx.x; i < num_points - 6; i += blockDim.x) {
     double a = 0.0;
