@@ -60,7 +60,7 @@ def dla_existence_prior(z_qso, prior_z_qsos, prior_dla_ind, params: Parameters =
     less_ind = prior_z_qsos < (z_qso + params.prior_z_qso_increase)
     this_num_dlas = int(np.count_nonzero(np.asarray(prior_dla_ind)[less_ind]))
     this_num_quasars = int(np.count_nonzero(less_ind))
-    with np.errstate(divide="ignore"):
+    with np.errstate(divide="ignore", invalid="ignore"):
         lp_dla = np.log(np.float64(this_num_dlas)) - np.log(np.float64(this_num_quasars))
         lp_no = np.log(np.float64(this_num_quasars - this_num_dlas)) - np.log(np.float64(this_num_quasars))
     return float(lp_dla), float(lp_no)

@@ -146,3 +146,23 @@ def test_process_qsos_drop_in(oracle):
     assert np.allclose(out["p_dlas"], 1 - out["model_posteriors"][:, 0])
     ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
     assert_parity(out, ref)
+
+
+def test_gpu_against_committed_goldens():
+    """The CUDA path against tests/golden/golden_v1.npz (voigt.c verbatim profiles; numpy / C+voigt.c
+    restatement log-likelihoods) -- nothing from oracle/ is executed here."""
+    import os
+    from tests.golden.make_golden import checksum
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_v1.npz"))
+    with DlaContext(k=20, num_samples=8) as ctx:
+        for i in range(6):
+            got = ctx.voigt(G["voigt_lambdas"], float(G["voigt_z"][i]), float(G["voigt_N"][i]), 3)
+            assert np.max(np.abs(got - G["voigt_profiles"][i])) <= 1e-12
+        got = ctx.voigt(G["voigt_lambdas"], float(G["voigt_z"][3]), 1e21, 31)
+        assert np.max(np.abs(got - G["voigt_profile_31"])) <= 1e-12
+    for name, Q, S, k, pre in (("tiny", 4, 64, 5, "tiny_"), ("config1", 2, 96, 20, "c1_")):
+        params, model, samples, sp, prepared = prepared_config(name, Q, S)
+        assert checksum(prepared) == str(G[pre + "checksum"])
+        got = _run_gpu(prepared, samples, k, S, sp.log_priors_dla, sp.log_priors_no_dla)
+        ref = {key[len(pre):]: G[key] for key in G.files if key.startswith(pre) and key != pre + "checksum"}
+        assert_parity(got, ref)
