@@ -27,11 +27,25 @@ static inline mxArray *mxCreateDoubleMatrix(mwSize m, mwSize n, mxComplexity c) 
   (void)c;
   mxArray *a = (mxArray *)malloc(sizeof(mxArray));
   a->m = m; a->n = n;
-  a->pr = (double *)calloc(m * n ? m * n : 1, sizeof(double));
+  a->pr = (double *)calloc((m * n) > 0 ? (m * n) : 1, sizeof(double));
   return a;
 }
 static inline void *mxMalloc(size_t n) { return malloc(n); }
 static inline void mxFree(void *p) { free(p); }
+
+/* Extra symbols used only by the product's MEX shims (gp_dla_detection_b200/mex/), so that the
+ * CPU test-suite can syntax/link-check them without MATLAB or Octave. */
+static inline mwSize mxGetM(const mxArray *a) { return a->m; }
+static inline mwSize mxGetN(const mxArray *a) { return a->n; }
+static inline mxArray *mxCreateDoubleScalar(double v) {
+  mxArray *a = mxCreateDoubleMatrix(1, 1, mxREAL);
+  a->pr[0] = v;
+  return a;
+}
+static inline int mxIsDouble(const mxArray *a) { (void)a; return 1; }
+static inline int mxIsComplex(const mxArray *a) { (void)a; return 0; }
+void mexErrMsgIdAndTxt(const char *id, const char *fmt, ...);
+int mexAtExit(void (*fn)(void));
 
 void mexFunction(int nlhs, mxArray *plhs[], int nrhs, const mxArray *prhs[]);
 #endif

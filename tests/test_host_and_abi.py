@@ -148,3 +148,21 @@ def test_world_size_2_gloo_host_gather():
     assert np.array_equal(merged["map_ind"], np.arange(11))
     assert np.array_equal(merged["sample_log_likelihoods_dla"][:, 0], np.arange(11.0))
     assert merged["nothing"] is None
+
+
+def test_mex_shims_compile_and_link_against_the_c_abi(tmp_path):
+    """No MATLAB/Octave here: compile the MEX gateways against the stand-in mex.h and link them with
+    libdla_b200.so, proving they only use symbols the header declares."""
+    import subprocess
+    stub = tmp_path / "stub.c"
+    stub.write_text('#include <stdarg.h>\n#include <stdlib.h>\n#include "mex.h"\n'
+                    'void mexErrMsgIdAndTxt(const char *id, const char *fmt, ...) { (void)id; (void)fmt; abort(); }\n'
+                    'int mexAtExit(void (*fn)(void)) { (void)fn; return 0; }\n')
+    env = dict(os.environ); env.pop("CC", None)
+    pkg = os.path.join(ROOT, "gp_dla_detection_b200")
+    _lib.load()
+    for src in ("voigt.c", "dla_eval_mex.c"):
+        out = tmp_path / (src + ".so")
+        subprocess.run(["gcc", "-Wall", "-Werror", "-shared", "-fPIC", os.path.join(pkg, "mex", src), str(stub),
+                        "-I", os.path.join(ROOT, "oracle", "shim"), "-I", os.path.join(ROOT, "include"),
+                        "-L", pkg, "-l:libdla_b200.so", "-Wl,--no-undefined", "-o", str(out)], check=True, env=env)
