@@ -33,7 +33,7 @@ N_PIX, K_RANK = 1217, 20
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--quasars", type=int, default=192, help="quasars per GPU per step")
@@ -58,7 +58,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.gpu), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+                                          "-i", str(self.gpu), "-lms", "100"], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -116,7 +116,8 @@ def cpu_reference_rate(prepared, samples, seconds: float, nthreads: int = 0):
     from oracle import oracle as O
     lib = O.load_c()
     have_ref = O.load_ref() is not None
-    cores = nthreads if nthreads > 0 else lib.oracle_max_threads()
+    # all host cores this process may use (torchrun exports OMP_NUM_THREADS=1: do not rely on it)
+    cores = nthreads if nthreads > 0 else max(lib.oracle_max_threads(), len(os.sched_getaffinity(0)))
     S = samples.offset_samples.shape[0]
     p = prepared[0]
     lp = (np.log(0.1), np.log(0.9))
