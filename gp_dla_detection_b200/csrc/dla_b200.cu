@@ -51,6 +51,7 @@ struct Inputs {
   const QuasarDesc* desc;
   const double *padded, *flux, *mu, *om, *nv, *M;
   const int32_t* pidx;
+  double2* pix4;  // packed {omega2, noise, mu, flux} per kept pixel (built per chunk on the device)
 };
 
 }  // namespace
@@ -69,7 +70,7 @@ struct dla_ctx {
   bool staged = false, ran = false;
   std::vector<QuasarDesc> h_desc;
   std::vector<Chunk> chunks;
-  DevBuf d_desc, d_padded, d_pidx, d_flux, d_mu, d_om, d_nv, d_M;
+  DevBuf d_desc, d_padded, d_pidx, d_flux, d_mu, d_om, d_nv, d_M, d_pix4;
   DevBuf d_sample_ll, d_ll_no, d_ll_dla, d_lp_no, d_lp_dla, d_post, d_map;
   // chunk workspace
   DevBuf d_W, d_U, d_bmat, d_aux, d_ll_chunk;
@@ -122,6 +123,10 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     dim3 grid((unsigned)(((int64_t)(ch.max_npad / 4) * dla::NCOL + 255) / 256), (unsigned)ch.nq);
     dla::build_bmat_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.M, B, k);
   }
+  {
+    dim3 grid((unsigned)((ch.max_npad + 255) / 256), (unsigned)ch.nq);
+    dla::pack_pixels_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
+  }
   if (time_it) CU_TRY(c, cudaEventRecord(c->ev[1], st));
   {
     const int raw_stride = (int)round_up(ch.max_P, 2);
@@ -129,7 +134,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     if (warps < 1) BAD_ARG(c, "a quasar has too many padded pixels for the Voigt kernel's shared-memory row");
     const size_t smem = (size_t)warps * raw_stride * 8 + 32 * 8;
     dla::voigt_weights_kernel<<<(unsigned)((int64_t)ch.nq * nsb), warps * 32, smem, st>>>(
-        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pidx, in.flux, in.mu, in.om, in.nv, W, U, aux,
+        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pidx, in.pix4, W, U, aux,
         num_lines, raw_stride);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(c->ev[2], st));
@@ -154,7 +159,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[3], c->ev[4])); c->timing.ms_reduce += ms;
     CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[4])); c->timing.ms_total += ms;
   }
-  c->timing.launches += (S > 0 && ll_dla) ? 4 : 3;
+  c->timing.launches += (S > 0 && ll_dla) ? 5 : 4;
   return DLA_OK;
 }
 
@@ -303,7 +308,7 @@ void dla_destroy(dla_ctx* c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
-                    &c->d_nv, &c->d_M, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
+                    &c->d_nv, &c->d_M, &c->d_pix4, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
                     &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk})
     b->release();
   for (auto& ev : c->ev)
@@ -363,9 +368,13 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
     d.log_prior_dla = log_prior_dla[q];
     d.log_prior_no_dla = log_prior_no_dla[q];
     const int32_t* pi = profile_index + pix_ptr[q];
-    for (int64_t j = 0; j < n; ++j)
+    bool ident = true;
+    for (int64_t j = 0; j < n; ++j) {
       if (pi[j] < 0 || pi[j] > P - 7 || (j > 0 && pi[j] <= pi[j - 1]))
         BAD_ARG(c, "dla_stage_batch: profile_index must be strictly increasing within [0, n_full)");
+      ident = ident && (pi[j] == j);
+    }
+    d.ident = ident ? 1 : 0;
   }
   // chunk plan: split so that W+U of a chunk fit the workspace budget, chunks balanced
   c->chunks.clear();
@@ -409,6 +418,7 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
   CU_TRY(c, up(c->d_desc, c->h_desc.data(), (size_t)Q * sizeof(QuasarDesc)));
   CU_TRY(c, up(c->d_padded, padded_wavelengths, (size_t)npadtot * 8));
   CU_TRY(c, up(c->d_pidx, profile_index, (size_t)npix * 4));
+  CU_TRY(c, c->d_pix4.ensure(std::max<size_t>((size_t)npix * 32, 32)));
   CU_TRY(c, up(c->d_flux, flux, (size_t)npix * 8));
   CU_TRY(c, up(c->d_mu, mu, (size_t)npix * 8));
   CU_TRY(c, up(c->d_om, omega2, (size_t)npix * 8));
@@ -461,7 +471,8 @@ int dla_run_staged(dla_ctx* c) {
   c->timing.h2d_bytes = keep_h2d;
   c->timing.ms_h2d = keep_ms_h2d;
   Inputs in{c->d_desc.as<QuasarDesc>(), c->d_padded.as<double>(), c->d_flux.as<double>(), c->d_mu.as<double>(),
-            c->d_om.as<double>(), c->d_nv.as<double>(), c->d_M.as<double>(), c->d_pidx.as<int32_t>()};
+            c->d_om.as<double>(), c->d_nv.as<double>(), c->d_M.as<double>(), c->d_pidx.as<int32_t>(),
+            c->d_pix4.as<double2>()};
   for (const Chunk& ch : c->chunks) {
     double* ll_chunk = c->p.store_sample_ll ? c->d_sample_ll.as<double>() + (int64_t)ch.q0 * S : c->d_ll_chunk.as<double>();
     int rc = launch_chunk(c, in, ch, S, c->p.k, c->p.num_lines, c->d_offset.as<double>(), c->d_nhi.as<double>(), ll_chunk,
@@ -575,13 +586,14 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
   hd.n = (int32_t)n;
   hd.P = (int32_t)n + 6;
   hd.npad = (int32_t)round_up(n, dla::KC);
+  hd.ident = 1;
   Chunk ch{0, 1, (int64_t)dla::TS * hd.npad, (int64_t)hd.npad * dla::NCOL, hd.npad, hd.P};
   int rc = ensure_workspace(c, ch.wu_doubles, ch.bmat_doubles, 1, 0, true);
   if (rc != DLA_OK) return rc;
-  DevBuf dd, dy, dmu, dM, dzero, dnv, dout;
+  DevBuf dd, dy, dmu, dM, dzero, dnv, dout, dpix;
   std::vector<double> zeros((size_t)n, 0.0);
   auto cleanup = [&]() {
-    for (DevBuf* b : {&dd, &dy, &dmu, &dM, &dzero, &dnv, &dout}) b->release();
+    for (DevBuf* b : {&dd, &dy, &dmu, &dM, &dzero, &dnv, &dout, &dpix}) b->release();
   };
 #define SEAM_TRY(call)                                                                     \
   do {                                                                                     \
@@ -599,6 +611,7 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
   SEAM_TRY(dzero.ensure((size_t)n * 8));
   SEAM_TRY(dnv.ensure((size_t)n * 8));
   SEAM_TRY(dout.ensure(64));
+  SEAM_TRY(dpix.ensure((size_t)n * 32));
   SEAM_TRY(cudaMemcpyAsync(dd.p, &hd, sizeof hd, cudaMemcpyHostToDevice, c->stream));
   SEAM_TRY(cudaMemcpyAsync(dy.p, y, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
   SEAM_TRY(cudaMemcpyAsync(dmu.p, mu, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
@@ -606,7 +619,7 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
   SEAM_TRY(cudaMemcpyAsync(dzero.p, zeros.data(), (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
   SEAM_TRY(cudaMemcpyAsync(dnv.p, d, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
   Inputs in{dd.as<QuasarDesc>(), dzero.as<double>(), dy.as<double>(), dmu.as<double>(), dzero.as<double>(),
-            dnv.as<double>(), dM.as<double>(), reinterpret_cast<const int32_t*>(dzero.p)};
+            dnv.as<double>(), dM.as<double>(), reinterpret_cast<const int32_t*>(dzero.p), dpix.as<double2>()};
   rc = launch_chunk(c, in, ch, 0, k, 1, dzero.as<double>(), dzero.as<double>(), c->d_ll_chunk.as<double>(),
                     dout.as<double>(), nullptr, nullptr, nullptr, nullptr, nullptr, false);
   if (rc != DLA_OK) {

@@ -66,6 +66,8 @@ struct LineConsts {
 };
 __device__ __constant__ LineConsts g_lines;
 
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
 // Per-quasar descriptor (device array, one per quasar of the staged batch).
 struct QuasarDesc {
   int64_t pix_off;   // offset of this quasar in the per-kept-pixel arrays
@@ -75,7 +77,7 @@ struct QuasarDesc {
   int32_t n;         // kept pixels
   int32_t P;         // padded points = n_full + 6
   int32_t npad;      // n rounded up to KC
-  int32_t pad_;
+  int32_t ident;     // profile_index[j] == j for all j (the as-written gather, process_qsos.m:180/:189)
   double min_z, max_z;
   double log_prior_dla, log_prior_no_dla;
 };
@@ -238,14 +240,102 @@ __device__ __forceinline__ void raw_transmission3(const double (&lambda)[NPIX], 
   for (int p = 0; p < NPIX; ++p) out[p] = exp_nonpos(-N * total[p], etab_s);
 }
 
+// shared-memory accessors on 32-bit shared-window addresses (keeps the address arithmetic out of
+// the inner loops)
+__device__ __forceinline__ double lds_f64(uint32_t a) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_f64(uint32_t a, double v) {
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
+}
+
+// K0b: interleave the four per-pixel inputs into one 32-byte record {omega2, noise, mu, flux}
+__global__ void pack_pixels_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ flux,
+                                   const double* __restrict__ mu, const double* __restrict__ omega2,
+                                   const double* __restrict__ noise_variance, double2* __restrict__ pix4) {
+  const QuasarDesc d = desc[q0 + blockIdx.y];
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= d.n) return;
+  const int64_t g = d.pix_off + j;
+  pix4[2 * g] = make_double2(omega2[g], noise_variance[g]);
+  pix4[2 * g + 1] = make_double2(mu[g], flux[g]);
+}
+
+// Phase 2 for two kept pixels (j, j+32) of one sample: 7-tap broadening, weights, row sums.
+// TAIL = false: both pixels exist for every lane (no predicates).  IDENT: profile_index[j] == j.
+template <bool TAIL, bool IDENT>
+__device__ __forceinline__ void k1_weights2(int j, int n, int npad, uint32_t raw_s, const int32_t* __restrict__ pidx,
+                                            const double2* __restrict__ px, double* __restrict__ wp,
+                                            double* __restrict__ up, double& q0acc, double& ldacc, double& dprod,
+                                            int& esum) {
+  double a[2], w[2], u[2];
+  bool live[2];
+  double2 p01[2], p23[2];
+  uint32_t ra[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int jj = j + 32 * h;
+    live[h] = TAIL ? (jj < n) : true;
+    const int jc = live[h] ? jj : 0;
+    p01[h] = __ldg(px + 2 * jc);
+    p23[h] = __ldg(px + 2 * jc + 1);
+    ra[h] = raw_s + 8u * (uint32_t)(IDENT ? jc : __ldg(pidx + jc));
+  }
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    double acc = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
+#pragma unroll
+    for (int t = 0; t < 7; ++t) acc = fma(lds_f64(ra[h] + 8u * t), dla_instrument_profile[t], acc);
+    a[h] = acc;
+  }
+  double dd[2];
+  bool okd[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const double a2 = a[h] * a[h];
+    dd[h] = fma(p01[h].x, a2, p01[h].y);              // process_qsos.m:193, :197
+    const double r = fma(-p23[h].x, a[h], p23[h].y);  // process_qsos.m:191, log_mvnpdf_low_rank.m:11
+    const double rinv = dla_fast_rcp(dd[h]);          // log_mvnpdf_low_rank.m:13
+    const double wv = a2 * rinv, uv = (a[h] * r) * rinv, qv = (r * r) * rinv;
+    // positive, normal and < 2^1022 (one integer compare on the high word)
+    okd[h] = (unsigned)(__double2hiint(dd[h]) - 0x00100000) < 0x7fc00000u;
+    if (TAIL) {
+      w[h] = live[h] ? wv : 0.0;
+      u[h] = live[h] ? uv : 0.0;
+      q0acc += live[h] ? qv : 0.0;
+      okd[h] = okd[h] || !live[h];
+      dd[h] = live[h] ? dd[h] : 1.0;
+    } else {
+      w[h] = wv;
+      u[h] = uv;
+      q0acc += qv;
+    }
+    dprod *= okd[h] ? dd[h] : 1.0;
+    const int hi = __double2hiint(dprod);
+    const int e = (hi >> 20) - 1023;
+    esum += e;
+    dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
+  }
+  if (!(okd[0] && okd[1])) {  // rare: zero / denormal / huge / NaN d -> exact log path
+    if (!okd[0]) ldacc += log(dd[0]);
+    if (!okd[1]) ldacc += log(dd[1]);
+  }
+  wp[0] = w[0];
+  up[0] = u[0];
+  if (!TAIL || j + 32 < npad) {
+    wp[8 * TS * 4] = w[1];
+    up[8 * TS * 4] = u[1];
+  }
+}
+
 __global__ void __launch_bounds__(K1_THREADS, 1)
 voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
                      const double* __restrict__ offset_samples, const double* __restrict__ nhi_samples,
                      const double* __restrict__ padded_wavelengths, const int32_t* __restrict__ profile_index,
-                     const double* __restrict__ flux, const double* __restrict__ mu,
-                     const double* __restrict__ omega2, const double* __restrict__ noise_variance,
-                     double* __restrict__ Wbuf, double* __restrict__ Ubuf, double* __restrict__ aux,
-                     int num_lines, int raw_stride) {
+                     const double2* __restrict__ pix4, double* __restrict__ Wbuf, double* __restrict__ Ubuf,
+                     double* __restrict__ aux, int num_lines, int raw_stride) {
   extern __shared__ double k1_smem[];
   const int ql = blockIdx.x / nsb, sb = blockIdx.x % nsb;
   const QuasarDesc d = desc[q0 + ql];
@@ -255,24 +345,29 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
   if (threadIdx.x < 32) etab_s[threadIdx.x] = g_lines.etab[threadIdx.x];
   __syncthreads();
   double* raw = k1_smem + 32 + (size_t)warp * raw_stride;
+  const uint32_t raw_s = smem_u32(raw);
 
   const double* lam = padded_wavelengths + d.pad_off;
   const int32_t* pidx = profile_index + d.pix_off;
-  const double* y_ = flux + d.pix_off;
-  const double* mu_ = mu + d.pix_off;
-  const double* om_ = omega2 + d.pix_off;
-  const double* nv_ = noise_variance + d.pix_off;
+  const double2* px = pix4 + 2 * d.pix_off;
   const int npc = d.npad >> 2;
   const int64_t S_pad = (int64_t)nsb * TS;
   double* Wq = Wbuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
   double* Uq = Ubuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
   double* auxq = aux + (int64_t)ql * 2 * S_pad;
+  const bool ident = d.ident != 0;
+  const int P = d.P, n = d.n, npad = d.npad;
 
   for (int srow = warp; srow < TS; srow += nwarps) {
     const int64_t s = (int64_t)sb * TS + srow;
-    const bool phantom = s > S;
-    const bool no_dla = (s == S);
-    if (!phantom && !no_dla) {
+    double* wp = Wq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
+    double* up = Uq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
+    if (s > S) {  // padding of the last sample block: zeros
+      for (int j = lane; j < npad; j += 32, wp += 8 * TS * 4, up += 8 * TS * 4) { *wp = 0.0; *up = 0.0; }
+      if (lane == 0) { auxq[s] = 0.0; auxq[S_pad + s] = 0.0; }
+      continue;
+    }
+    if (s != S) {  // s == S is the no-DLA pseudo-sample: profile == 1, no Voigt (process_qsos.m:150-152)
       // process_qsos.m:163-165: min + (max - min) * offset, separately rounded
       const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), offset_samples[s]));
       const double N = nhi_samples[s];
@@ -281,18 +376,28 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
         double mult3[3];  // voigt.c:278-279 (registers: every index below is static)
 #pragma unroll
         for (int j = 0; j < 3; ++j) mult3[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
-        for (int i0 = 0; i0 < d.P; i0 += 64) {  // warp-uniform trip count (warp reduction inside)
-          const int ia = i0 + lane, ib = ia + 32;
-          const double l2[2] = {__ldg(lam + min(ia, d.P - 1)), __ldg(lam + min(ib, d.P - 1))};
+        const double* lp = lam + lane;
+        uint32_t rs = raw_s + 8u * lane;
+        int i0 = 0;
+        for (; i0 + 64 <= P; i0 += 64, lp += 64, rs += 512) {  // full groups: no clamps, no predicates
+          const double l2[2] = {__ldg(lp), __ldg(lp + 32)};
           double r2[2];
           raw_transmission3<2>(l2, mult3, N, etab_s, r2);
-          if (ia < d.P) raw[ia] = r2[0];
-          if (ib < d.P) raw[ib] = r2[1];
+          sts_f64(rs, r2[0]);
+          sts_f64(rs + 256, r2[1]);
+        }
+        if (i0 < P) {  // tail group (warp-uniform branch; the warp reduction inside needs all lanes)
+          const int ia = i0 + lane, ib = ia + 32;
+          const double l2[2] = {__ldg(lam + min(ia, P - 1)), __ldg(lam + min(ib, P - 1))};
+          double r2[2];
+          raw_transmission3<2>(l2, mult3, N, etab_s, r2);
+          if (ia < P) sts_f64(rs, r2[0]);
+          if (ib < P) sts_f64(rs + 256, r2[1]);
         }
       } else {
         double mult[DLA_MAX_LINES];
         for (int j = 0; j < num_lines; ++j) mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
-        for (int i = lane; i < d.P; i += 32) raw[i] = raw_transmission(__ldg(lam + i), mult, N, num_lines, etab_s);
+        for (int i = lane; i < P; i += 32) raw[i] = raw_transmission(__ldg(lam + i), mult, N, num_lines, etab_s);
       }
     }
     __syncwarp();
@@ -301,59 +406,36 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     // with the exponents summed as integers -> one log per lane per sample instead of one per pixel
     double dprod = 1.0;
     int esum = 0;
-    // this lane's first element of the [pixel/4][64][4] tile layout; +32 pixels = +8 pixel groups
-    double* wp = Wq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
-    double* up = Uq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
-    // two pixels per lane per iteration (j and j+32): independent chains, loads issued up front
-    for (int j = lane; j < d.npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4) {
-      double w[2] = {0.0, 0.0}, u[2] = {0.0, 0.0}, dd[2] = {1.0, 1.0};
-      bool live[2], okd[2];
-      double om2[2], nv2[2], mu2[2], y2v[2], a[2];
-      int pi2[2];
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int jj = j + 32 * h;
-        live[h] = (jj < d.n) && !phantom;
-        const int jc = live[h] ? jj : 0;
-        pi2[h] = no_dla ? 0 : __ldg(pidx + jc);
-        om2[h] = __ldg(om_ + jc); nv2[h] = __ldg(nv_ + jc); mu2[h] = __ldg(mu_ + jc); y2v[h] = __ldg(y_ + jc);
-      }
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        a[h] = 1.0;
-        if (!no_dla) {  // warp-uniform
-          const double* rp = raw + pi2[h];
-          double acc = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
-#pragma unroll
-          for (int t = 0; t < 7; ++t) acc = fma(rp[t], dla_instrument_profile[t], acc);
-          a[h] = acc;
+    if (s == S) {
+      // a == 1 for every pixel
+      for (int j = lane; j < npad; j += 32, wp += 8 * TS * 4, up += 8 * TS * 4) {
+        double w = 0.0, u = 0.0;
+        if (j < n) {
+          const double2 p01 = __ldg(px + 2 * j), p23 = __ldg(px + 2 * j + 1);
+          const double d_ = p01.x + p01.y;
+          const double r = p23.y - p23.x;
+          const double rinv = dla_fast_rcp(d_);
+          w = rinv;
+          u = r * rinv;
+          q0acc = fma(r * r, rinv, q0acc);
+          ldacc += log(d_);
         }
+        *wp = w;
+        *up = u;
       }
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const double a2 = a[h] * a[h];
-        const double d_ = fma(om2[h], a2, nv2[h]);    // process_qsos.m:193, :197
-        const double r = fma(-mu2[h], a[h], y2v[h]);  // process_qsos.m:191, log_mvnpdf_low_rank.m:11
-        const double rinv = dla_fast_rcp(d_);         // log_mvnpdf_low_rank.m:13
-        const double wv = a2 * rinv, uv = (a[h] * r) * rinv, qv = (r * r) * rinv;
-        w[h] = live[h] ? wv : 0.0;
-        u[h] = live[h] ? uv : 0.0;
-        q0acc += live[h] ? qv : 0.0;
-        // positive, normal and < 2^1022 (one integer compare on the high word)
-        okd[h] = (unsigned)(__double2hiint(d_) - 0x00100000) < 0x7fc00000u;
-        dd[h] = d_;
-        dprod *= (live[h] && okd[h]) ? d_ : 1.0;
-        const int hi = __double2hiint(dprod);
-        const int e = (hi >> 20) - 1023;
-        esum += e;
-        dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
+    } else {
+      int j = lane;
+      if (ident) {
+        for (; (j - lane) + 64 <= n; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
+          k1_weights2<false, true>(j, n, npad, raw_s, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
+        for (; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
+          k1_weights2<true, true>(j, n, npad, raw_s, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
+      } else {
+        for (; (j - lane) + 64 <= n; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
+          k1_weights2<false, false>(j, n, npad, raw_s, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
+        for (; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
+          k1_weights2<true, false>(j, n, npad, raw_s, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
       }
-      if ((live[0] && !okd[0]) || (live[1] && !okd[1])) {  // rare: zero / denormal / huge / NaN d
-        if (live[0] && !okd[0]) ldacc += log(dd[0]);
-        if (live[1] && !okd[1]) ldacc += log(dd[1]);
-      }
-      wp[0] = w[0]; up[0] = u[0];
-      if (j + 32 < d.npad) { wp[8 * TS * 4] = w[1]; up[8 * TS * 4] = u[1]; }
     }
     ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
 #pragma unroll
@@ -363,7 +445,7 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     }
     if (lane == 0) {
       auxq[s] = q0acc;
-      auxq[S_pad + s] = phantom ? 0.0 : ldacc;
+      auxq[S_pad + s] = ldacc;
     }
     __syncwarp();
   }
@@ -392,7 +474,6 @@ __global__ void voigt_single_kernel(const double* __restrict__ lambdas, int num_
 // ----------------------------------------------------------------------------------------------
 // K2: DMMA contraction + Cholesky epilogue.
 // ----------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
