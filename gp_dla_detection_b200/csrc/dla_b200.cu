@@ -129,7 +129,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   }
   if (time_it) CU_TRY(c, cudaEventRecord(c->ev[1], st));
   {
-    const int raw_stride = (int)round_up(ch.max_P, 2);
+    const int raw_stride = (int)round_up(ch.max_P, 2) + 2;  // +2: the 16-byte window loads of the tail may touch one double past P
     const int warps = k1_warps_for(raw_stride);
     if (warps < 1) BAD_ARG(c, "a quasar has too many padded pixels for the Voigt kernel's shared-memory row");
     const size_t smem = (size_t)warps * raw_stride * 8 + 32 * 8;

@@ -263,32 +263,44 @@ __global__ void pack_pixels_kernel(const QuasarDesc* __restrict__ desc, int q0, 
   pix4[2 * g + 1] = make_double2(mu[g], flux[g]);
 }
 
-// Phase 2 for two kept pixels (j, j+32) of one sample: 7-tap broadening, weights, row sums.
-// TAIL = false: both pixels exist for every lane (no predicates).  IDENT: profile_index[j] == j.
+// Phase 2 for two ADJACENT kept pixels (j, j+1; j even) of one sample: 7-tap broadening, weights,
+// row sums.  TAIL = false: both pixels exist (no predicates).  IDENT: profile_index[j] == j, so the
+// two 7-tap windows are the 8 consecutive doubles raw[j..j+7] = four 16-byte shared loads.
 template <bool TAIL, bool IDENT>
-__device__ __forceinline__ void k1_weights2(int j, int n, int npad, uint32_t raw_s, const int32_t* __restrict__ pidx,
-                                            const double2* __restrict__ px, double* __restrict__ wp,
-                                            double* __restrict__ up, double& q0acc, double& ldacc, double& dprod,
-                                            int& esum) {
+__device__ __forceinline__ void k1_weights2(int j, int n, const double* __restrict__ raw,
+                                            const int32_t* __restrict__ pidx, const double2* __restrict__ px,
+                                            double* __restrict__ wp, double* __restrict__ up, double& q0acc,
+                                            double& ldacc, double& dprod, int& esum) {
   double a[2], w[2], u[2];
   bool live[2];
   double2 p01[2], p23[2];
-  uint32_t ra[2];
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
-    const int jj = j + 32 * h;
-    live[h] = TAIL ? (jj < n) : true;
-    const int jc = live[h] ? jj : 0;
+    live[h] = TAIL ? (j + h < n) : true;
+    const int jc = live[h] ? j + h : 0;
     p01[h] = __ldg(px + 2 * jc);
     p23[h] = __ldg(px + 2 * jc + 1);
-    ra[h] = raw_s + 8u * (uint32_t)(IDENT ? jc : __ldg(pidx + jc));
   }
+  if (IDENT) {
+    const double2* rw = reinterpret_cast<const double2*>(raw + (TAIL ? min(j, n - 1) & ~1 : j));
+    const double2 r0 = rw[0], r1 = rw[1], r2 = rw[2], r3 = rw[3];
+    const double win[8] = {r0.x, r0.y, r1.x, r1.y, r2.x, r2.y, r3.x, r3.y};
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    double acc = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
+    for (int h = 0; h < 2; ++h) {
+      double acc = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
 #pragma unroll
-    for (int t = 0; t < 7; ++t) acc = fma(lds_f64(ra[h] + 8u * t), dla_instrument_profile[t], acc);
-    a[h] = acc;
+      for (int t = 0; t < 7; ++t) acc = fma(win[h + t], dla_instrument_profile[t], acc);
+      a[h] = acc;
+    }
+  } else {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const double* rp = raw + __ldg(pidx + (live[h] ? j + h : 0));
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 7; ++t) acc = fma(rp[t], dla_instrument_profile[t], acc);
+      a[h] = acc;
+    }
   }
   double dd[2];
   bool okd[2];
@@ -322,12 +334,8 @@ __device__ __forceinline__ void k1_weights2(int j, int n, int npad, uint32_t raw
     if (!okd[0]) ldacc += log(dd[0]);
     if (!okd[1]) ldacc += log(dd[1]);
   }
-  wp[0] = w[0];
-  up[0] = u[0];
-  if (!TAIL || j + 32 < npad) {
-    wp[8 * TS * 4] = w[1];
-    up[8 * TS * 4] = u[1];
-  }
+  *reinterpret_cast<double2*>(wp) = make_double2(w[0], w[1]);
+  *reinterpret_cast<double2*>(up) = make_double2(u[0], u[1]);
 }
 
 __global__ void __launch_bounds__(K1_THREADS, 1)
@@ -360,10 +368,14 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
 
   for (int srow = warp; srow < TS; srow += nwarps) {
     const int64_t s = (int64_t)sb * TS + srow;
-    double* wp = Wq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
-    double* up = Uq + ((lane >> 2) * TS + srow) * 4 + (lane & 3);
+    // lane L owns the adjacent pixel pair (2L, 2L+1) of every 64-pixel group
+    double* wp = Wq + ((lane >> 1) * TS + srow) * 4 + 2 * (lane & 1);
+    double* up = Uq + ((lane >> 1) * TS + srow) * 4 + 2 * (lane & 1);
     if (s > S) {  // padding of the last sample block: zeros
-      for (int j = lane; j < npad; j += 32, wp += 8 * TS * 4, up += 8 * TS * 4) { *wp = 0.0; *up = 0.0; }
+      for (int j = 2 * lane; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4) {
+        *reinterpret_cast<double2*>(wp) = make_double2(0.0, 0.0);
+        *reinterpret_cast<double2*>(up) = make_double2(0.0, 0.0);
+      }
       if (lane == 0) { auxq[s] = 0.0; auxq[S_pad + s] = 0.0; }
       continue;
     }
@@ -376,23 +388,22 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
         double mult3[3];  // voigt.c:278-279 (registers: every index below is static)
 #pragma unroll
         for (int j = 0; j < 3; ++j) mult3[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
-        const double* lp = lam + lane;
-        uint32_t rs = raw_s + 8u * lane;
+        const double* lp = lam + 2 * lane;
+        double2* rs = reinterpret_cast<double2*>(raw) + lane;
         int i0 = 0;
-        for (; i0 + 64 <= P; i0 += 64, lp += 64, rs += 512) {  // full groups: no clamps, no predicates
-          const double l2[2] = {__ldg(lp), __ldg(lp + 32)};
+        for (; i0 + 64 <= P; i0 += 64, lp += 64, rs += 32) {  // full groups: no clamps, no predicates
+          const double l2[2] = {__ldg(lp), __ldg(lp + 1)};
           double r2[2];
           raw_transmission3<2>(l2, mult3, N, etab_s, r2);
-          sts_f64(rs, r2[0]);
-          sts_f64(rs + 256, r2[1]);
+          *rs = make_double2(r2[0], r2[1]);
         }
         if (i0 < P) {  // tail group (warp-uniform branch; the warp reduction inside needs all lanes)
-          const int ia = i0 + lane, ib = ia + 32;
+          const int ia = i0 + 2 * lane, ib = ia + 1;
           const double l2[2] = {__ldg(lam + min(ia, P - 1)), __ldg(lam + min(ib, P - 1))};
           double r2[2];
           raw_transmission3<2>(l2, mult3, N, etab_s, r2);
-          if (ia < P) sts_f64(rs, r2[0]);
-          if (ib < P) sts_f64(rs + 256, r2[1]);
+          if (ia < P) raw[ia] = r2[0];
+          if (ib < P) raw[ib] = r2[1];
         }
       } else {
         double mult[DLA_MAX_LINES];
@@ -408,33 +419,36 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     int esum = 0;
     if (s == S) {
       // a == 1 for every pixel
-      for (int j = lane; j < npad; j += 32, wp += 8 * TS * 4, up += 8 * TS * 4) {
-        double w = 0.0, u = 0.0;
-        if (j < n) {
-          const double2 p01 = __ldg(px + 2 * j), p23 = __ldg(px + 2 * j + 1);
-          const double d_ = p01.x + p01.y;
-          const double r = p23.y - p23.x;
-          const double rinv = dla_fast_rcp(d_);
-          w = rinv;
-          u = r * rinv;
-          q0acc = fma(r * r, rinv, q0acc);
-          ldacc += log(d_);
+      for (int j = 2 * lane; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4) {
+        double w[2] = {0.0, 0.0}, u[2] = {0.0, 0.0};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          if (j + h < n) {
+            const double2 p01 = __ldg(px + 2 * (j + h)), p23 = __ldg(px + 2 * (j + h) + 1);
+            const double d_ = p01.x + p01.y;
+            const double r = p23.y - p23.x;
+            const double rinv = dla_fast_rcp(d_);
+            w[h] = rinv;
+            u[h] = r * rinv;
+            q0acc = fma(r * r, rinv, q0acc);
+            ldacc += log(d_);
+          }
         }
-        *wp = w;
-        *up = u;
+        *reinterpret_cast<double2*>(wp) = make_double2(w[0], w[1]);
+        *reinterpret_cast<double2*>(up) = make_double2(u[0], u[1]);
       }
     } else {
-      int j = lane;
+      int j = 2 * lane;
       if (ident) {
-        for (; (j - lane) + 64 <= n; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
-          k1_weights2<false, true>(j, n, npad, raw_s, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
+        for (; (j - 2 * lane) + 64 <= n; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
+          k1_weights2<false, true>(j, n, raw, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
         for (; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
-          k1_weights2<true, true>(j, n, npad, raw_s, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
+          k1_weights2<true, true>(j, n, raw, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
       } else {
-        for (; (j - lane) + 64 <= n; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
-          k1_weights2<false, false>(j, n, npad, raw_s, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
+        for (; (j - 2 * lane) + 64 <= n; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
+          k1_weights2<false, false>(j, n, raw, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
         for (; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
-          k1_weights2<true, false>(j, n, npad, raw_s, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
+          k1_weights2<true, false>(j, n, raw, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
       }
     }
     ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
