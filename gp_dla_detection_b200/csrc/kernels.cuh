@@ -266,21 +266,32 @@ __global__ void pack_pixels_kernel(const QuasarDesc* __restrict__ desc, int q0, 
 // Phase 2 for two ADJACENT kept pixels (j, j+1; j even) of one sample: 7-tap broadening, weights,
 // row sums.  TAIL = false: both pixels exist (no predicates).  IDENT: profile_index[j] == j, so the
 // two 7-tap windows are the 8 consecutive doubles raw[j..j+7] = four 16-byte shared loads.
+struct PixPair {
+  double2 p01[2], p23[2];  // {omega2, noise}, {mu, flux} of the two pixels
+};
+template <bool TAIL>
+__device__ __forceinline__ PixPair k1_load_pair(int j, int n, const double2* __restrict__ px) {
+  PixPair q;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int jc = (!TAIL || j + h < n) ? j + h : 0;
+    q.p01[h] = __ldg(px + 2 * jc);
+    q.p23[h] = __ldg(px + 2 * jc + 1);
+  }
+  return q;
+}
+
 template <bool TAIL, bool IDENT>
 __device__ __forceinline__ void k1_weights2(int j, int n, const double* __restrict__ raw,
-                                            const int32_t* __restrict__ pidx, const double2* __restrict__ px,
+                                            const int32_t* __restrict__ pidx, const PixPair& q,
                                             double* __restrict__ wp, double* __restrict__ up, double& q0acc,
                                             double& ldacc, double& dprod, int& esum) {
   double a[2], w[2], u[2];
   bool live[2];
-  double2 p01[2], p23[2];
+  const double2 (&p01)[2] = q.p01;
+  const double2 (&p23)[2] = q.p23;
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    live[h] = TAIL ? (j + h < n) : true;
-    const int jc = live[h] ? j + h : 0;
-    p01[h] = __ldg(px + 2 * jc);
-    p23[h] = __ldg(px + 2 * jc + 1);
-  }
+  for (int h = 0; h < 2; ++h) live[h] = TAIL ? (j + h < n) : true;
   if (IDENT) {
     const double2* rw = reinterpret_cast<const double2*>(raw + (TAIL ? min(j, n - 1) & ~1 : j));
     const double2 r0 = rw[0], r1 = rw[1], r2 = rw[2], r3 = rw[3];
@@ -391,8 +402,11 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
         const double* lp = lam + 2 * lane;
         double2* rs = reinterpret_cast<double2*>(raw) + lane;
         int i0 = 0;
+        double la = 0.0, lb = 0.0;
+        if (64 <= P) { la = __ldg(lp); lb = __ldg(lp + 1); }
         for (; i0 + 64 <= P; i0 += 64, lp += 64, rs += 32) {  // full groups: no clamps, no predicates
-          const double l2[2] = {__ldg(lp), __ldg(lp + 1)};
+          const double l2[2] = {la, lb};
+          if (i0 + 128 <= P) { la = __ldg(lp + 64); lb = __ldg(lp + 65); }  // next group's wavelengths
           double r2[2];
           raw_transmission3<2>(l2, mult3, N, etab_s, r2);
           *rs = make_double2(r2[0], r2[1]);
@@ -439,16 +453,21 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
       }
     } else {
       int j = 2 * lane;
-      if (ident) {
-        for (; (j - 2 * lane) + 64 <= n; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
-          k1_weights2<false, true>(j, n, raw, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
-        for (; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
-          k1_weights2<true, true>(j, n, raw, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
-      } else {
-        for (; (j - 2 * lane) + 64 <= n; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
-          k1_weights2<false, false>(j, n, raw, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
-        for (; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4)
-          k1_weights2<true, false>(j, n, raw, pidx, px, wp, up, q0acc, ldacc, dprod, esum);
+      const int nfull = (n / 64) * 64;  // pixels covered by predicate-free groups
+      if (j < nfull) {                  // software-pipelined: the next group's inputs load under this group's math
+        PixPair cur = k1_load_pair<false>(j, n, px);
+        for (; j < nfull; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4) {
+          const bool more = (j + 64 < nfull);
+          const PixPair nxt = k1_load_pair<false>(more ? j + 64 : j, n, px);
+          if (ident) k1_weights2<false, true>(j, n, raw, pidx, cur, wp, up, q0acc, ldacc, dprod, esum);
+          else k1_weights2<false, false>(j, n, raw, pidx, cur, wp, up, q0acc, ldacc, dprod, esum);
+          cur = nxt;
+        }
+      }
+      for (; j < npad; j += 64, wp += 16 * TS * 4, up += 16 * TS * 4) {
+        const PixPair cur = k1_load_pair<true>(j, n, px);
+        if (ident) k1_weights2<true, true>(j, n, raw, pidx, cur, wp, up, q0acc, ldacc, dprod, esum);
+        else k1_weights2<true, false>(j, n, raw, pidx, cur, wp, up, q0acc, ldacc, dprod, esum);
       }
     }
     ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
