@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -44,6 +45,7 @@ struct Chunk {
   int q0, nq;
   int64_t wu_doubles, bmat_doubles;
   int max_npad, max_P;
+  bool all_ident;  // every quasar of the chunk uses the as-written gather (profile_index[j] == j)
 };
 
 // Device-side views of one staged batch.
@@ -63,8 +65,11 @@ struct dla_ctx {
   std::string err;
   cudaEvent_t ev[8]{};
   // hypothesis set
-  DevBuf d_offset, d_nhi;
+  // (sorted by offset once: the hypotheses of a warp are then neighbours in z; d_perm maps a
+  //  sorted position back to the caller's sample index)
+  DevBuf d_offset, d_nhi, d_perm, d_etab256;
   bool have_samples = false;
+  bool force_pixel_lane_k1 = false;  // DLA_B200_K1=pixel: always use voigt_weights_kernel
   // staged batch
   int64_t Q = 0;
   bool staged = false, ran = false;
@@ -109,7 +114,7 @@ static int k1_warps_for(int raw_stride) {
 
 // Runs K0..K3 for one chunk of quasars on ctx->stream. sample_ll_chunk: [nq][S].
 static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S, int k, int num_lines,
-                        const double* d_offset, const double* d_nhi, double* sample_ll_chunk, double* ll_no,
+                        const double* d_offset, const double* d_nhi, const int32_t* d_perm, double* sample_ll_chunk, double* ll_no,
                         double* ll_dla, double* lp_no, double* lp_dla, double* post, int32_t* map_index,
                         bool time_it) {
   const int nsb = (int)((S + 1 + dla::TS - 1) / dla::TS);
@@ -128,7 +133,10 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     dla::pack_pixels_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(c->ev[1], st));
-  {
+  if (ch.all_ident && num_lines == 3 && !c->force_pixel_lane_k1) {
+    dla::voigt_weights_lane_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K1S_THREADS, 0, st>>>(
+        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_etab256.as<double>(), W, U, aux);
+  } else {
     const int raw_stride = (int)round_up(ch.max_P, 2) + 2;  // +2: the 16-byte window loads of the tail may touch one double past P
     const int warps = k1_warps_for(raw_stride);
     if (warps < 1) BAD_ARG(c, "a quasar has too many padded pixels for the Voigt kernel's shared-memory row");
@@ -141,7 +149,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   {
     const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
     dla::contract_chol_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K2_THREADS, smem, st>>>(
-        in.desc, ch.q0, nsb, S, W, U, B, aux, sample_ll_chunk, ll_no, k);
+        in.desc, ch.q0, nsb, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(c->ev[3], st));
   if (S > 0 && ll_dla) {
@@ -272,6 +280,9 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     h.vnear2 = (DLA_FADD_XNEAR * sqrt(2.0) * sigma) * (DLA_FADD_XNEAR * sqrt(2.0) * sigma);
     h.inv_sqrt2_sigma = 1.0 / (sqrt(2.0) * sigma);
     h.c_cgs = DLA_C_CGS;
+    h.k256 = 256.0 * 1.4426950408889634074;
+    h.nln2hi256 = -6.93147180369123816490e-01 / 256.0;
+    h.nln2lo256 = -1.90821492927058770002e-10 / 256.0;
     h.k32 = 32.0 * 1.4426950408889634074;  // 32 / ln 2
     h.magic = 6755399441055744.0;           // 1.5 * 2^52: adding it rounds to the nearest integer
     h.nln2hi32 = -6.93147180369123816490e-01 / 32.0;  // exact scalings of the hi/lo split of ln 2
@@ -294,6 +305,12 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
       h.hi_256 = hi_of(256.0);
     }
     CREATE_TRY(cudaMemcpyToSymbol(dla::g_lines, &h, sizeof h));
+    double e256[256];
+    for (int i = 0; i < 256; ++i) e256[i] = exp2(i / 256.0);
+    CREATE_TRY(c->d_etab256.ensure(sizeof e256));
+    CREATE_TRY(cudaMemcpy(c->d_etab256.p, e256, sizeof e256, cudaMemcpyHostToDevice));
+    const char* k1 = getenv("DLA_B200_K1");
+    c->force_pixel_lane_k1 = k1 && strcmp(k1, "pixel") == 0;
   }
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
@@ -307,7 +324,7 @@ void dla_destroy(dla_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
-  for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
+  for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_perm, &c->d_etab256, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
                     &c->d_nv, &c->d_M, &c->d_pix4, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
                     &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk})
     b->release();
@@ -324,9 +341,27 @@ int dla_set_samples(dla_ctx* c, const double* offset_samples, const double* nhi_
   const size_t bytes = (size_t)std::max<int64_t>(1, c->p.num_samples) * 8;
   CU_TRY(c, c->d_offset.ensure(bytes));
   CU_TRY(c, c->d_nhi.ensure(bytes));
+  CU_TRY(c, c->d_perm.ensure((size_t)std::max<int64_t>(1, c->p.num_samples) * 4));
   if (c->p.num_samples > 0) {
-    CU_TRY(c, cudaMemcpyAsync(c->d_offset.p, offset_samples, (size_t)c->p.num_samples * 8, cudaMemcpyHostToDevice, c->stream));
-    CU_TRY(c, cudaMemcpyAsync(c->d_nhi.p, nhi_samples, (size_t)c->p.num_samples * 8, cudaMemcpyHostToDevice, c->stream));
+    // stable sort by offset (NaN last): the result of a hypothesis does not depend on its position
+    // up to the series-length choice it shares with its warp (<= 3e-13 relative either way)
+    const int64_t S = c->p.num_samples;
+    std::vector<int32_t> perm((size_t)S);
+    for (int64_t i = 0; i < S; ++i) perm[(size_t)i] = (int32_t)i;
+    std::stable_sort(perm.begin(), perm.end(), [&](int32_t a, int32_t b) {
+      const double x = offset_samples[a], y = offset_samples[b];
+      if (x != x) return false;
+      if (y != y) return true;
+      return x < y;
+    });
+    std::vector<double> so((size_t)S), sn((size_t)S);
+    for (int64_t i = 0; i < S; ++i) {
+      so[(size_t)i] = offset_samples[perm[(size_t)i]];
+      sn[(size_t)i] = nhi_samples[perm[(size_t)i]];
+    }
+    CU_TRY(c, cudaMemcpyAsync(c->d_offset.p, so.data(), (size_t)S * 8, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(c->d_nhi.p, sn.data(), (size_t)S * 8, cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(c->d_perm.p, perm.data(), (size_t)S * 4, cudaMemcpyHostToDevice, c->stream));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
   }
   c->have_samples = true;
@@ -386,7 +421,7 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
     const long double target = total / nch;
     int64_t q = 0;
     while (q < Q) {
-      Chunk ch{(int)q, 0, 0, 0, 0, 0};
+      Chunk ch{(int)q, 0, 0, 0, 0, 0, true};
       long double acc = 0;
       while (q < Q) {
         QuasarDesc& d = c->h_desc[(size_t)q];
@@ -398,6 +433,7 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
         ch.bmat_doubles += (int64_t)d.npad * dla::NCOL;
         ch.max_npad = std::max(ch.max_npad, (int)d.npad);
         ch.max_P = std::max(ch.max_P, (int)d.P);
+        ch.all_ident = ch.all_ident && d.ident != 0;
         acc += b;
         ++ch.nq;
         ++q;
@@ -475,7 +511,8 @@ int dla_run_staged(dla_ctx* c) {
             c->d_pix4.as<double2>()};
   for (const Chunk& ch : c->chunks) {
     double* ll_chunk = c->p.store_sample_ll ? c->d_sample_ll.as<double>() + (int64_t)ch.q0 * S : c->d_ll_chunk.as<double>();
-    int rc = launch_chunk(c, in, ch, S, c->p.k, c->p.num_lines, c->d_offset.as<double>(), c->d_nhi.as<double>(), ll_chunk,
+    int rc = launch_chunk(c, in, ch, S, c->p.k, c->p.num_lines, c->d_offset.as<double>(), c->d_nhi.as<double>(),
+                          c->d_perm.as<int32_t>(), ll_chunk,
                           c->d_ll_no.as<double>(), c->d_ll_dla.as<double>(), c->d_lp_no.as<double>(),
                           c->d_lp_dla.as<double>(), c->d_post.as<double>(), c->d_map.as<int32_t>(), true);
     if (rc != DLA_OK) return rc;
@@ -587,7 +624,7 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
   hd.P = (int32_t)n + 6;
   hd.npad = (int32_t)round_up(n, dla::KC);
   hd.ident = 1;
-  Chunk ch{0, 1, (int64_t)dla::TS * hd.npad, (int64_t)hd.npad * dla::NCOL, hd.npad, hd.P};
+  Chunk ch{0, 1, (int64_t)dla::TS * hd.npad, (int64_t)hd.npad * dla::NCOL, hd.npad, hd.P, false};
   int rc = ensure_workspace(c, ch.wu_doubles, ch.bmat_doubles, 1, 0, true);
   if (rc != DLA_OK) return rc;
   DevBuf dd, dy, dmu, dM, dzero, dnv, dout, dpix;
@@ -620,7 +657,8 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
   SEAM_TRY(cudaMemcpyAsync(dnv.p, d, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
   Inputs in{dd.as<QuasarDesc>(), dzero.as<double>(), dy.as<double>(), dmu.as<double>(), dzero.as<double>(),
             dnv.as<double>(), dM.as<double>(), reinterpret_cast<const int32_t*>(dzero.p), dpix.as<double2>()};
-  rc = launch_chunk(c, in, ch, 0, k, 1, dzero.as<double>(), dzero.as<double>(), c->d_ll_chunk.as<double>(),
+  rc = launch_chunk(c, in, ch, 0, k, 1, dzero.as<double>(), dzero.as<double>(),
+                    reinterpret_cast<const int32_t*>(dzero.p), c->d_ll_chunk.as<double>(),
                     dout.as<double>(), nullptr, nullptr, nullptr, nullptr, nullptr, false);
   if (rc != DLA_OK) {
     cleanup();

@@ -63,6 +63,8 @@ struct LineConsts {
   double etab[32];             // 2^(i/32)
   // high 32 bits of the velocity^2 thresholds for |x| < 16 (core), < 64, < 256 (series length)
   int hi_near, hi_64, hi_256, pad_;
+  // exp for the sample-per-lane kernel: t = (256 m + i) ln2/256 + r, |r| <= ln2/512, Taylor degree 4
+  double k256, nln2hi256, nln2lo256;
 };
 __device__ __constant__ LineConsts g_lines;
 
@@ -484,6 +486,254 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
   }
 }
 
+// ----------------------------------------------------------------------------------------------
+// K1 (sample-per-lane form): the same arithmetic as voigt_weights_kernel, laid out the other way
+// round.  A lane owns ONE hypothesis and walks a segment of the spectrum; the 32 lanes of a warp
+// hold 32 hypotheses that are adjacent in z (the hypothesis set is sorted by offset once, in
+// dla_set_samples), so
+//   * every per-pixel input (wavelength, omega2, noise, mu, flux) is a warp-uniform load,
+//   * the Lyman line cores of the 32 lanes fall on (nearly) the same pixels: the series-length
+//     decision is warp-uniform almost everywhere and the rare core path runs converged,
+//   * the 7-tap broadening window lives in registers (no shared-memory row, no second pass),
+//   * W/U leave as 32-byte per-lane records that are contiguous across the warp in the
+//     DMMA-fragment layout [pixel/4][64 samples][4 pixels],
+//   * q0 and log|D| are private running sums (one cross-segment reduction per CTA at the end).
+// CTA = 64 hypotheses (one sample block) x K1S_NSEG spectrum segments.  Requires the as-written
+// gather (profile_index[j] == j) and num_lines == 3; anything else takes voigt_weights_kernel.
+// Hypotheses s >= S of the last block (the no-DLA pseudo-sample s == S and the padding rows) run
+// with N = 0, which gives a == 1 exactly (process_qsos.m:150-152).
+// ----------------------------------------------------------------------------------------------
+constexpr int K1S_NSEG = 4;
+constexpr int K1S_THREADS = TS * K1S_NSEG;
+
+// exp(t), t <= 0, result >= 2^-1020 (t is clamped at -707: a transmission of 1e-307 and one of 0
+// are the same number to every consumer: a^2 underflows either way).  NaN propagates.
+__device__ __forceinline__ double exp_tab256(double t, const double* __restrict__ etab_s) {
+  t = (t < -707.0) ? -707.0 : t;
+  const double kd = fma(t, g_lines.k256, g_lines.magic);
+  const int ki = __double2loint(kd);
+  const double kf = kd - g_lines.magic;
+  double r = fma(kf, g_lines.nln2hi256, t);
+  r = fma(kf, g_lines.nln2lo256, r);
+  double p = fma(r, 1.0 / 24.0, 1.0 / 6.0);
+  p = fma(p, r, 0.5);
+  p = fma(p, r, 1.0);
+  p = fma(p, r, 1.0);
+  const double tv = etab_s[ki & 255];  // 2^(i/256) in [1, 2): adding m to its exponent field stays normal
+  const double sc = __hiloint2double(__double2hiint(tv) + ((ki >> 8) << 20), __double2loint(tv));
+  return p * sc;
+}
+
+// reciprocal: MUFU.RCP64H seed (relative error e <= 2^-20) + one cubic step r(1 + e + e^2): e^3 <= 2^-60
+__device__ __forceinline__ double rcp_cubic(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  e = fma(e, e, e);
+  return fma(r, e, r);
+}
+
+template <int NT>
+__device__ __forceinline__ double wing_term_n(double sp, int j, double ncw, double total) {
+  double G = g_lines.gq[NT - 1];
+#pragma unroll
+  for (int n = NT - 2; n >= 0; --n) G = fma(G, sp, g_lines.gq[n]);
+  if (NT == 7) G -= (g_lines.y2T[j] * sp) * fma(g_lines.fiveT, sp, 1.0);
+  else G = fma(-g_lines.y2T[j], sp, G);
+  return fma(ncw * sp, G, total);
+}
+
+// raw transmission exp(-N sum_j tau_j) of NPIX wavelengths for this lane's hypothesis
+// (voigt.c:282-292).  ncw[j] = -N cwT_j.  Must be called by all 32 lanes.
+template <int NPIX>
+__device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const double (&mult)[3],
+                                         const double (&ncw)[3], double N, const double* etab_s,
+                                         double (&out)[NPIX]) {
+  double sp[NPIX][3];
+  int minhi = 0x7fffffff;
+#pragma unroll
+  for (int p = 0; p < NPIX; ++p) {
+    double v2[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double velocity = __dsub_rn(__dmul_rn(lambda[p], mult[j]), g_lines.c_cgs);  // voigt.c:287
+      v2[j] = velocity * velocity;
+      minhi = min(minhi, __double2hiint(v2[j]));
+    }
+    const double p01 = v2[0] * v2[1];
+    const double rr = rcp_cubic(p01 * v2[2]);
+    const double r01 = rr * v2[2];
+    sp[p][2] = rr * p01;
+    sp[p][0] = r01 * v2[1];
+    sp[p][1] = r01 * v2[0];
+  }
+  const int wmin = __reduce_min_sync(0xffffffffu, minhi);
+  double total[NPIX];  // = -N sum_j tau_j
+#pragma unroll
+  for (int p = 0; p < NPIX; ++p) total[p] = 0.0;
+  if (wmin >= g_lines.hi_256) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int p = 0; p < NPIX; ++p) total[p] = wing_term_n<3>(sp[p][j], j, ncw[j], total[p]);
+  } else if (wmin >= g_lines.hi_64) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int p = 0; p < NPIX; ++p) total[p] = wing_term_n<4>(sp[p][j], j, ncw[j], total[p]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int p = 0; p < NPIX; ++p) total[p] = wing_term_n<7>(sp[p][j], j, ncw[j], total[p]);
+    if (minhi < g_lines.hi_near) {  // a line core within this lane's pixels: exact two-regime path
+#pragma unroll
+      for (int p = 0; p < NPIX; ++p) {
+        double t = 0.0;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) t += line_tau_slow(lambda[p], mult[j], j);
+        total[p] = -N * t;
+      }
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < NPIX; ++p) out[p] = exp_tab256(total[p], etab_s);
+}
+
+// weights of the four kept pixels 4g..4g+3 from the 10-point window raw[4g .. 4g+9]
+template <bool TAIL>
+__device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int n, const double2* __restrict__ px,
+                                             double* __restrict__ wp, double* __restrict__ up, double& q0acc,
+                                             double& ldacc, double& dprod, int& esum) {
+  double w[4], u[4], dd[4];
+  bool allok = true;
+#pragma unroll
+  for (int h = 0; h < 4; ++h) {
+    const int j = 4 * g + h;
+    const bool live = !TAIL || j < n;
+    const int jc = live ? j : 0;
+    const double2 p01 = __ldg(px + 2 * jc);      // {omega2, noise}
+    const double2 p23 = __ldg(px + 2 * jc + 1);  // {mu, flux}
+    double a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
+#pragma unroll
+    for (int t = 0; t < 7; ++t) a = fma(win[h + t], dla_instrument_profile[t], a);
+    const double a2 = a * a;
+    const double d_ = fma(p01.x, a2, p01.y);     // process_qsos.m:193, :197
+    const double r = fma(-p23.x, a, p23.y);      // process_qsos.m:191, log_mvnpdf_low_rank.m:11
+    const double rinv = rcp_cubic(d_);           // log_mvnpdf_low_rank.m:13
+    const double gq_ = a * rinv;
+    const double wv = a * gq_, uv = r * gq_, rr = r * rinv;
+    // d within 2^+-200 (one integer compare on the high word): the running product of four such
+    // factors and a value in [1,2) cannot leave the normal range
+    bool ok = (unsigned)(__double2hiint(d_) - ((1023 - 200) << 20)) < (unsigned)(400 << 20);
+    if (TAIL) {
+      w[h] = live ? wv : 0.0;
+      u[h] = live ? uv : 0.0;
+      q0acc = live ? fma(r, rr, q0acc) : q0acc;
+      ok = ok || !live;
+      dd[h] = live ? d_ : 1.0;
+    } else {
+      w[h] = wv;
+      u[h] = uv;
+      q0acc = fma(r, rr, q0acc);
+      dd[h] = d_;
+    }
+    allok = allok && ok;
+    dprod *= ok ? dd[h] : 1.0;
+  }
+  if (!allok) {  // rare: zero / denormal / huge / NaN d -> exact log
+#pragma unroll
+    for (int h = 0; h < 4; ++h)
+      if (!((unsigned)(__double2hiint(dd[h]) - ((1023 - 200) << 20)) < (unsigned)(400 << 20))) ldacc += log(dd[h]);
+  }
+  {
+    const int hi = __double2hiint(dprod);
+    const int e = (hi >> 20) - 1023;
+    esum += e;
+    dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
+  }
+  reinterpret_cast<double2*>(wp)[0] = make_double2(w[0], w[1]);
+  reinterpret_cast<double2*>(wp)[1] = make_double2(w[2], w[3]);
+  reinterpret_cast<double2*>(up)[0] = make_double2(u[0], u[1]);
+  reinterpret_cast<double2*>(up)[1] = make_double2(u[2], u[3]);
+}
+
+__global__ void __launch_bounds__(K1S_THREADS, 2)
+voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
+                          const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
+                          const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
+                          const double* __restrict__ etab256, double* __restrict__ Wbuf,
+                          double* __restrict__ Ubuf, double* __restrict__ aux) {
+  __shared__ double etab_s[256];
+  __shared__ double red_s[K1S_NSEG][TS][2];
+  const int ql = blockIdx.x / nsb, sb = blockIdx.x % nsb;
+  const QuasarDesc d = desc[q0 + ql];
+  const int tid = threadIdx.x;
+  etab_s[tid & 255] = etab256[tid & 255];
+  __syncthreads();
+  const int srow = tid & (TS - 1), seg = tid / TS;
+  const int64_t s = (int64_t)sb * TS + srow;
+  const bool real = s < S;
+  // process_qsos.m:163-165: min + (max - min) * offset, separately rounded
+  const double off = real ? offset_sorted[s] : 0.0;
+  const double N = real ? nhi_sorted[s] : 0.0;
+  const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), off));
+  const double opz = __dadd_rn(1.0, z);
+  double mult[3], ncw[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;  // voigt.c:278-279
+    ncw[j] = -N * g_lines.cwT[j];
+  }
+  const double* lam = padded_wavelengths + d.pad_off;
+  const double2* px = pix4 + 2 * d.pix_off;
+  const int npc = d.npad >> 2, n = d.n, Pm1 = d.P - 1;
+  const int g0 = (int)(((int64_t)seg * npc) / K1S_NSEG), g1 = (int)(((int64_t)(seg + 1) * npc) / K1S_NSEG);
+  const int gfull = n >> 2;  // groups [0, gfull) have four live pixels
+  const int64_t S_pad = (int64_t)nsb * TS;
+  double* wp = Wbuf + d.wu_off + ((int64_t)sb * npc + g0) * (TS * 4) + srow * 4;
+  double* up = Ubuf + d.wu_off + ((int64_t)sb * npc + g0) * (TS * 4) + srow * 4;
+
+  double q0acc = 0.0, ldacc = 0.0, dprod = 1.0;
+  int esum = 0;
+  double win[10];
+#pragma unroll
+  for (int t = 0; t < 10; ++t) win[t] = 0.0;
+  // step st computes raw[b .. b+3], b = 4 (g0 + st) - 2, and (from st = 2 on) emits group g0 + st - 2,
+  // whose window raw[4g .. 4g+9] is then complete
+  const int nsteps = g1 - g0 + 2;
+  for (int st = 0; st < nsteps; ++st) {
+    const int b = 4 * (g0 + st) - 2;
+    double l4[4], r4[4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) l4[h] = __ldg(lam + min(max(b + h, 0), Pm1));
+    raw_lane<4>(l4, mult, ncw, N, etab_s, r4);
+#pragma unroll
+    for (int t = 0; t < 6; ++t) win[t] = win[t + 4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) win[6 + h] = r4[h];
+    if (st >= 2) {
+      const int g = g0 + st - 2;
+      if (g < gfull) weights_lane<false>(win, g, n, px, wp, up, q0acc, ldacc, dprod, esum);
+      else weights_lane<true>(win, g, n, px, wp, up, q0acc, ldacc, dprod, esum);
+      wp += TS * 4;
+      up += TS * 4;
+    }
+  }
+  ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
+  red_s[seg][srow][0] = q0acc;
+  red_s[seg][srow][1] = ldacc;
+  __syncthreads();
+  if (tid < TS) {
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int g = 0; g < K1S_NSEG; ++g) { a0 += red_s[g][tid][0]; a1 += red_s[g][tid][1]; }
+    double* auxq = aux + (int64_t)ql * 2 * S_pad;
+    auxq[s] = a0;
+    auxq[S_pad + s] = a1;
+  }
+}
+
 // Single-profile seam (dla_voigt = the voigt MEX, voigt.c:253-304). One CTA.
 __global__ void voigt_single_kernel(const double* __restrict__ lambdas, int num_points, double z, double N,
                                     int num_lines, double* __restrict__ raw, double* __restrict__ profile) {
@@ -604,6 +854,7 @@ __global__ void __launch_bounds__(K2_THREADS, 1)
 contract_chol_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
                      const double* __restrict__ Wbuf, const double* __restrict__ Ubuf,
                      const double* __restrict__ bmat, const double* __restrict__ aux,
+                     const int32_t* __restrict__ perm /* sorted position -> caller's sample index */,
                      double* __restrict__ sample_ll /* [Qc][S] chunk-local */,
                      double* __restrict__ ll_no_dla /* [Q] batch-global */, int k) {
   extern __shared__ __align__(128) unsigned char k2_smem_raw[];
@@ -703,7 +954,7 @@ contract_chol_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     const double q0v = auxq[s], ldv = auxq[S_pad + s];
     const double lp = chol_logp_quad(Cs + (size_t)srow * LDC, k, t, q0v, ldv, d.n);
     if (t == 0) {
-      if (s < S) sample_ll[(int64_t)ql * S + s] = lp;
+      if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
       else if (s == S) ll_no_dla[q0 + ql] = lp;
     }
   }
