@@ -300,13 +300,13 @@ def run_ours(args):
                 "launches_per_step": int(tm["chunks"]), "ms_per_step": 1e3 * t_contract,
                 "step_frac_end_to_end": (flop_per_step / (dev_s / args.steps) / 1e12) / dgemm_tflops}
     wu_bytes = 16.0 * S * n_sum                                    # W and U written once (fp64)
-    roofline_voigt = {"kernel": "voigt_weights_kernel (K1)", "bound": "fp64 vector pipe (reported vs hbm as north_star asks)",
+    roofline_voigt = {"kernel": "voigt_weights_lane_kernel (K1, sample-per-lane)", "bound": "fp64 vector pipe (reported vs hbm as north_star asks)",
                       "achieved": wu_bytes / t_voigt / 1e9, "peak": hbm_peak, "unit": "GB/s",
                       "frac": wu_bytes / t_voigt / 1e9 / hbm_peak,
                       "faddeeva_evals_per_s": 3.0 * S * float((batch.n_full + 6).sum()) / t_voigt,
                       "ms_per_step": 1e3 * t_voigt,
                       "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"}
-    dominant = "K1 voigt_weights_kernel" if t_voigt > t_contract else "K2 contract_chol_kernel"
+    dominant = "K1 voigt_weights_lane_kernel" if t_voigt > t_contract else "K2 contract_chol_kernel"
 
     if rank == 0:
         cpu = None

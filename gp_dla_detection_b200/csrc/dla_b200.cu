@@ -70,6 +70,8 @@ struct dla_ctx {
   DevBuf d_offset, d_nhi, d_perm, d_etab256;
   bool have_samples = false;
   bool force_pixel_lane_k1 = false;  // DLA_B200_K1=pixel: always use voigt_weights_kernel
+  bool force_tile_k2 = false;        // DLA_B200_K2=tile: one CTA per tile (contract_chol_kernel)
+  int num_sms = 148;
   // staged batch
   int64_t Q = 0;
   bool staged = false, ran = false;
@@ -146,7 +148,12 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
         num_lines, raw_stride);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(c->ev[2], st));
-  {
+  if (!c->force_tile_k2) {
+    const int64_t ntiles = (int64_t)ch.nq * nsb;
+    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
+    dla::contract_chol_persistent_kernel<<<grid, dla::K2P_THREADS, dla::K2P_SMEM_BYTES, st>>>(
+        in.desc, ch.q0, nsb, (int)ntiles, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k);
+  } else {
     const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
     dla::contract_chol_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K2_THREADS, smem, st>>>(
         in.desc, ch.q0, nsb, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k);
@@ -309,11 +316,16 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     for (int i = 0; i < 256; ++i) e256[i] = exp2(i / 256.0);
     CREATE_TRY(c->d_etab256.ensure(sizeof e256));
     CREATE_TRY(cudaMemcpy(c->d_etab256.p, e256, sizeof e256, cudaMemcpyHostToDevice));
+    const char* k2 = getenv("DLA_B200_K2");
+    c->force_tile_k2 = k2 && strcmp(k2, "tile") == 0;
+    c->num_sms = prop.multiProcessorCount;
     const char* k1 = getenv("DLA_B200_K1");
     c->force_pixel_lane_k1 = k1 && strcmp(k1, "pixel") == 0;
   }
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
+  CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)dla::K2P_SMEM_BYTES));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #undef CREATE_TRY
   *out = c;

@@ -800,6 +800,7 @@ __device__ __forceinline__ int tri(int i, int l) { return ((i * (i + 1)) >> 1) +
 // t = L^-1 v and the corner as q0 - t^T t = r^T K^-1 r; log|B| = sum log pivots
 // (log_mvnpdf_low_rank.m:23-32).  No shared-memory traffic after the initial load.
 // row[0..210): vech(G), row[VOFF..VOFF+k): v.  Returns log p on all four lanes.
+template <bool SYNC_AFTER_LOAD = false>
 __device__ __forceinline__ double chol_logp_quad(const double* __restrict__ row, int k, int t, double q0, double ld,
                                                  int n) {
   constexpr int NB = KMAX;      // border row index (20)
@@ -822,6 +823,7 @@ __device__ __forceinline__ double chol_logp_quad(const double* __restrict__ row,
       A[r][l] = v;
     }
   }
+  if (SYNC_AFTER_LOAD) asm volatile("bar.sync 1, 256;" ::: "memory");  // the C tile may be overwritten from here on
   double pprod = 1.0;  // product of the pivots this lane is responsible for (j = t mod 4): <= 5 factors
 #pragma unroll
   for (int j = 0; j < NB; ++j) {
@@ -956,6 +958,159 @@ contract_chol_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     if (t == 0) {
       if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
       else if (s == S) ll_no_dla[q0 + ql] = lp;
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// K2, persistent form.  One CTA per SM walks the (quasar, sample block) tiles t = blockIdx.x,
+// blockIdx.x + gridDim.x, ...  Warp 8 is the producer: its elected lane streams the K-chunks of
+// ALL of the CTA's tiles, back to back, through a ring of K2P_STAGES shared-memory stages
+// (1-D TMA bulk copies, `full` mbarriers with transaction counts); the eight DMMA warps release
+// a stage with one arrive per warp on its `empty` mbarrier.  There is no CTA-wide barrier in the
+// main loop, and the first chunks of the next tile are already in flight while the current tile
+// runs its Cholesky epilogue out of a dedicated C buffer.
+// ----------------------------------------------------------------------------------------------
+constexpr int K2P_KC = 8;                                  // pixels per stage
+constexpr int K2P_STAGES = 4;
+constexpr int K2P_W_DOUBLES = TS * K2P_KC;                 // 512
+constexpr int K2P_B_DOUBLES = K2P_KC * NCOL;               // 1920
+constexpr int K2P_STAGE_DOUBLES = 2 * K2P_W_DOUBLES + K2P_B_DOUBLES;  // 2944 = 23552 B
+constexpr int K2P_C_DOUBLES = TS * LDC;                    // 15488 = 123904 B
+constexpr int K2P_CONSUMER_WARPS = 8;
+constexpr int K2P_THREADS = (K2P_CONSUMER_WARPS + 4) * 32;  // two DMMA warpgroups + the producer's warpgroup
+constexpr size_t K2P_SMEM_BYTES = (size_t)(K2P_STAGES * K2P_STAGE_DOUBLES + K2P_C_DOUBLES) * 8 + 2 * K2P_STAGES * 8;
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void consumer_bar_sync() {  // the 256 DMMA threads only
+  asm volatile("bar.sync 1, 256;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(K2P_THREADS, 1)
+contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int ntiles, int64_t S,
+                                const double* __restrict__ Wbuf, const double* __restrict__ Ubuf,
+                                const double* __restrict__ bmat, const double* __restrict__ aux,
+                                const int32_t* __restrict__ perm, double* __restrict__ sample_ll,
+                                double* __restrict__ ll_no_dla, int k) {
+  extern __shared__ __align__(128) unsigned char k2_smem_raw[];
+  double* smem = reinterpret_cast<double*>(k2_smem_raw);
+  double* Cs = smem + (size_t)K2P_STAGES * K2P_STAGE_DOUBLES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(Cs + K2P_C_DOUBLES);
+  uint64_t* empty = full + K2P_STAGES;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int s = 0; s < K2P_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], K2P_CONSUMER_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  // 384 threads x 168 registers fill the register file; the producer's warpgroup hands most of its
+  // share back so that the DMMA warps can hold the accumulator tile and the register-resident Cholesky
+  if (warp >= K2P_CONSUMER_WARPS) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    // ---------------- producer ----------------
+    if (warp == K2P_CONSUMER_WARPS && lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int ql = t / nsb, sb = t - ql * nsb;
+        const QuasarDesc* dp = desc + q0 + ql;
+        const int npad = dp->npad;
+        const int64_t wu_off = dp->wu_off + (int64_t)sb * (npad >> 2) * (TS * 4);
+        const double* Wsrc = Wbuf + wu_off;
+        const double* Usrc = Ubuf + wu_off;
+        const double* Bsrc = bmat + dp->bmat_off;
+        const int nchunks = npad / K2P_KC;
+        for (int c = 0; c < nchunks; ++c, ++it) {
+          const int st = it % K2P_STAGES;
+          mbar_wait(&empty[st], ((it / K2P_STAGES) & 1) ^ 1);  // passes at once on the first lap
+          double* dst = smem + (size_t)st * K2P_STAGE_DOUBLES;
+          mbar_expect_tx(&full[st], K2P_STAGE_DOUBLES * 8);
+          bulk_g2s(dst, Wsrc + (int64_t)c * K2P_W_DOUBLES, K2P_W_DOUBLES * 8, &full[st]);
+          bulk_g2s(dst + K2P_W_DOUBLES, Usrc + (int64_t)c * K2P_W_DOUBLES, K2P_W_DOUBLES * 8, &full[st]);
+          bulk_g2s(dst + 2 * K2P_W_DOUBLES, Bsrc + (int64_t)c * K2P_B_DOUBLES, K2P_B_DOUBLES * 8, &full[st]);
+        }
+      }
+    }
+    return;
+  }
+
+  // ---------------- DMMA warps: 4 row groups of 16 samples x 2 column halves of 15 tiles ----------------
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+  const int mrow = warp & 3, half = warp >> 2;
+  constexpr int TPW = NT / 2;
+  uint32_t it = 0;
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int ql = t / nsb, sb = t - ql * nsb;
+    const int n = desc[q0 + ql].n;
+    const int nchunks = desc[q0 + ql].npad / K2P_KC;
+    double acc[TPW][4];
+#pragma unroll
+    for (int j = 0; j < TPW; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0;
+
+    for (int c = 0; c < nchunks; ++c, ++it) {
+      const int st = it % K2P_STAGES;
+      mbar_wait(&full[st], (it / K2P_STAGES) & 1);
+      const double* Ws = smem + (size_t)st * K2P_STAGE_DOUBLES;
+      const double* Us = Ws + K2P_W_DOUBLES;
+      const double* Bs = Us + K2P_W_DOUBLES;
+#pragma unroll
+      for (int kc = 0; kc < K2P_KC / 4; ++kc) {
+        const double aw0 = Ws[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+        const double aw1 = Ws[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+        const double* bp = Bs + kc * (NCOL * 4) + (half * TPW) * 32 + lane;
+        if (half == 0) {
+#pragma unroll
+          for (int j = 0; j < TPW; ++j) {
+            const double b = bp[j * 32];
+            dmma884(acc[j][0], acc[j][1], aw0, b);
+            dmma884(acc[j][2], acc[j][3], aw1, b);
+          }
+        } else {
+          const double au0 = Us[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+          const double au1 = Us[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+#pragma unroll
+          for (int j = 0; j < TPW; ++j) {
+            const double b = bp[j * 32];
+            const bool isv = (TPW + j) >= PHI_TILES;
+            dmma884(acc[j][0], acc[j][1], isv ? au0 : aw0, b);
+            dmma884(acc[j][2], acc[j][3], isv ? au1 : aw1, b);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[st]);
+    }
+
+    // accumulators -> C tile (its readers of the previous tile passed the barrier below)
+    {
+      const int r0 = (2 * mrow) * 8 + (lane >> 2);
+      const int cbase = (half * TPW) * 8 + 2 * (lane & 3);
+#pragma unroll
+      for (int j = 0; j < TPW; ++j) {
+        double* p0 = Cs + (size_t)r0 * LDC + cbase + j * 8;
+        double* p1 = p0 + 8 * LDC;
+        p0[0] = acc[j][0]; p0[1] = acc[j][1];
+        p1[0] = acc[j][2]; p1[1] = acc[j][3];
+      }
+    }
+    consumer_bar_sync();
+    {
+      const int srow = tid >> 2, q4 = tid & 3;
+      const int64_t s = (int64_t)sb * TS + srow;
+      const int64_t S_pad = (int64_t)nsb * TS;
+      const double* auxq = aux + (int64_t)ql * 2 * S_pad;
+      const double q0v = auxq[s], ldv = auxq[S_pad + s];
+      const double lp = chol_logp_quad<true>(Cs + (size_t)srow * LDC, k, q4, q0v, ldv, n);
+      if (q4 == 0) {
+        if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
+        else if (s == S) ll_no_dla[q0 + ql] = lp;
+      }
     }
   }
 }
