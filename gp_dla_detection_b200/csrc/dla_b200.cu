@@ -72,6 +72,7 @@ struct dla_ctx {
   bool force_pixel_lane_k1 = false;  // DLA_B200_K1=pixel: always use voigt_weights_kernel
   bool force_tile_k2 = false;        // DLA_B200_K2=tile: one CTA per tile (contract_chol_kernel)
   int num_sms = 148;
+  int k1_sb_per_cta = 1;
   // staged batch
   int64_t Q = 0;
   bool staged = false, ran = false;
@@ -136,8 +137,14 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   }
   if (time_it) CU_TRY(c, cudaEventRecord(c->ev[1], st));
   if (ch.all_ident && num_lines == 3 && !c->force_pixel_lane_k1) {
-    dla::voigt_weights_lane_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K1S_THREADS, 0, st>>>(
-        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_etab256.as<double>(), W, U, aux);
+    const int sb_per_cta = c->k1_sb_per_cta;
+    const int nsbg = (nsb + sb_per_cta - 1) / sb_per_cta;
+    const int lam_cap = (int)round_up(ch.max_P, 2);
+    const size_t smem = ((size_t)lam_cap + 4 * (size_t)ch.max_npad) * 8;
+    if (smem > 100 * 1024) BAD_ARG(c, "a quasar has too many pixels for the Voigt kernel's shared-memory staging");
+    dla::voigt_weights_lane_kernel<<<(unsigned)((int64_t)ch.nq * nsbg), dla::K1S_THREADS, smem, st>>>(
+        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_etab256.as<double>(), W, U, aux,
+        sb_per_cta, lam_cap);
   } else {
     const int raw_stride = (int)round_up(ch.max_P, 2) + 2;  // +2: the 16-byte window loads of the tail may touch one double past P
     const int warps = k1_warps_for(raw_stride);
@@ -319,6 +326,7 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     const char* k2 = getenv("DLA_B200_K2");
     c->force_tile_k2 = k2 && strcmp(k2, "tile") == 0;
     c->num_sms = prop.multiProcessorCount;
+    if (const char* e = getenv("DLA_B200_K1_SB")) c->k1_sb_per_cta = std::max(1, atoi(e));
     const char* k1 = getenv("DLA_B200_K1");
     c->force_pixel_lane_k1 = k1 && strcmp(k1, "pixel") == 0;
   }
@@ -326,6 +334,7 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)dla::K2P_SMEM_BYTES));
+  CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #undef CREATE_TRY
   *out = c;

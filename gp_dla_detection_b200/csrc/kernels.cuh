@@ -602,7 +602,7 @@ __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const dou
 
 // weights of the four kept pixels 4g..4g+3 from the 10-point window raw[4g .. 4g+9]
 template <bool TAIL>
-__device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int n, const double2* __restrict__ px,
+__device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int n, const double2* px /* shared */,
                                              double* __restrict__ wp, double* __restrict__ up, double& q0acc,
                                              double& ldacc, double& dprod, int& esum) {
   double w[4], u[4], dd[4];
@@ -612,8 +612,8 @@ __device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int
     const int j = 4 * g + h;
     const bool live = !TAIL || j < n;
     const int jc = live ? j : 0;
-    const double2 p01 = __ldg(px + 2 * jc);      // {omega2, noise}
-    const double2 p23 = __ldg(px + 2 * jc + 1);  // {mu, flux}
+    const double2 p01 = px[2 * jc];      // {omega2, noise}
+    const double2 p23 = px[2 * jc + 1];  // {mu, flux}
     double a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
 #pragma unroll
     for (int t = 0; t < 7; ++t) a = fma(win[h + t], dla_instrument_profile[t], a);
@@ -663,15 +663,28 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
                           const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
                           const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
                           const double* __restrict__ etab256, double* __restrict__ Wbuf,
-                          double* __restrict__ Ubuf, double* __restrict__ aux) {
+                          double* __restrict__ Ubuf, double* __restrict__ aux, int sb_per_cta, int lam_cap) {
+  // shared: the quasar's padded wavelengths [lam_cap] and packed pixel records [n][4] (every lane of
+  // the CTA reads the same addresses: broadcast LDS instead of global loads), then the exp table
+  extern __shared__ __align__(16) double k1s_smem[];
   __shared__ double etab_s[256];
   __shared__ double red_s[K1S_NSEG][TS][2];
-  const int ql = blockIdx.x / nsb, sb = blockIdx.x % nsb;
+  const int nsbg = (nsb + sb_per_cta - 1) / sb_per_cta;
+  const int ql = blockIdx.x / nsbg, sbg = blockIdx.x % nsbg;
   const QuasarDesc d = desc[q0 + ql];
   const int tid = threadIdx.x;
+  double* lam_s = k1s_smem;
+  double2* px_s = reinterpret_cast<double2*>(k1s_smem + lam_cap);
   etab_s[tid & 255] = etab256[tid & 255];
+  {
+    const double* lam_g = padded_wavelengths + d.pad_off;
+    for (int i = tid; i < d.P; i += K1S_THREADS) lam_s[i] = __ldg(lam_g + i);
+    const double2* px_g = pix4 + 2 * d.pix_off;
+    for (int i = tid; i < 2 * d.n; i += K1S_THREADS) px_s[i] = __ldg(px_g + i);
+  }
   __syncthreads();
   const int srow = tid & (TS - 1), seg = tid / TS;
+  for (int sb = sbg * sb_per_cta; sb < min(nsb, (sbg + 1) * sb_per_cta); ++sb) {
   const int64_t s = (int64_t)sb * TS + srow;
   const bool real = s < S;
   // process_qsos.m:163-165: min + (max - min) * offset, separately rounded
@@ -685,8 +698,8 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
     mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;  // voigt.c:278-279
     ncw[j] = -N * g_lines.cwT[j];
   }
-  const double* lam = padded_wavelengths + d.pad_off;
-  const double2* px = pix4 + 2 * d.pix_off;
+  const double* lam = lam_s;
+  const double2* px = px_s;
   const int npc = d.npad >> 2, n = d.n, Pm1 = d.P - 1;
   const int g0 = (int)(((int64_t)seg * npc) / K1S_NSEG), g1 = (int)(((int64_t)(seg + 1) * npc) / K1S_NSEG);
   const int gfull = n >> 2;  // groups [0, gfull) have four live pixels
@@ -706,7 +719,7 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
     const int b = 4 * (g0 + st) - 2;
     double l4[4], r4[4];
 #pragma unroll
-    for (int h = 0; h < 4; ++h) l4[h] = __ldg(lam + min(max(b + h, 0), Pm1));
+    for (int h = 0; h < 4; ++h) l4[h] = lam[min(max(b + h, 0), Pm1)];
     raw_lane<4>(l4, mult, ncw, N, etab_s, r4);
 #pragma unroll
     for (int t = 0; t < 6; ++t) win[t] = win[t + 4];
@@ -731,6 +744,8 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
     double* auxq = aux + (int64_t)ql * 2 * S_pad;
     auxq[s] = a0;
     auxq[S_pad + s] = a1;
+  }
+  __syncthreads();  // red_s is reused by the next sample block
   }
 }
 
