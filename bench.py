@@ -265,7 +265,11 @@ def run_ours(args):
     value = Q * world * args.steps / dev_s
 
     # ---- end-to-end leg: dla_eval_batch, pinned host buffers in, host buffers out ---------------
-    outputs = ctx._alloc_outputs(Q)
+    def pinned_alloc(shape, dtype):
+        t = torch.empty(shape, dtype={np.float64: torch.float64, np.int32: torch.int32}[np.dtype(dtype).type]).pin_memory()
+        keep.append(t)
+        return t.numpy()
+    outputs = ctx._alloc_outputs(Q, alloc=pinned_alloc)
     ctx.eval_batch(batch, sp.log_priors_dla, sp.log_priors_no_dla, outputs)
     barrier()
     t0 = time.perf_counter()
@@ -275,7 +279,7 @@ def run_ours(args):
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     tm = ctx.timing()
     e2e = {"value": Q * world * args.steps / e2e_s, "unit": METRIC, "h2d_bytes_per_step": int(tm["h2d_bytes"]),
-           "d2h_bytes_per_step": int(tm["d2h_bytes"]), "timed": "wall clock around K dla_eval_batch calls, max over ranks",
+           "d2h_bytes_per_step": int(tm["d2h_bytes"]), "timed": "wall clock around K dla_eval_batch calls (pinned host buffers in and out; copies of one quasar chunk overlap the kernels of another), max over ranks",
            "host_prep": "per-quasar numpy preparation (process_qsos.m:102-180) is outside the timed region"}
     assert np.all(np.isfinite(out["log_likelihoods_dla"]))
 

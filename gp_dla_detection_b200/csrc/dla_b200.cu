@@ -63,7 +63,17 @@ struct dla_ctx {
   dla_params p{};
   cudaStream_t stream = nullptr;
   std::string err;
+  cudaStream_t s_in = nullptr, s_out = nullptr;  // copy streams: H2D ahead of, D2H behind, the compute stream
   cudaEvent_t ev[8]{};
+  std::vector<cudaEvent_t> ev_time;   // 5 timing events per chunk
+  std::vector<cudaEvent_t> ev_sync;   // 2 ordering events per chunk: inputs resident, kernels done
+  std::vector<Chunk> chunk_copy;      // host-side copy of the plan the events belong to
+  // host pointers of the batch being staged chunk by chunk (valid during dla_eval_batch only)
+  struct HostIn {
+    const int64_t *pix_ptr, *pad_ptr;
+    const double *padded, *flux, *mu, *om, *nv, *M;
+    const int32_t* pidx;
+  } hin{};
   // hypothesis set
   // (sorted by offset once: the hypotheses of a warp are then neighbours in z; d_perm maps a
   //  sorted position back to the caller's sample index)
@@ -119,14 +129,15 @@ static int k1_warps_for(int raw_stride) {
 static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S, int k, int num_lines,
                         const double* d_offset, const double* d_nhi, const int32_t* d_perm, double* sample_ll_chunk, double* ll_no,
                         double* ll_dla, double* lp_no, double* lp_dla, double* post, int32_t* map_index,
-                        bool time_it) {
+                        cudaEvent_t* tev /* 5 timing events or nullptr */) {
+  const bool time_it = tev != nullptr;
   const int nsb = (int)((S + 1 + dla::TS - 1) / dla::TS);
   double* W = c->d_W.as<double>();
   double* U = c->d_U.as<double>();
   double* B = c->d_bmat.as<double>();
   double* aux = c->d_aux.as<double>();
   cudaStream_t st = c->stream;
-  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[0], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[0], st));
   {
     dim3 grid((unsigned)(((int64_t)(ch.max_npad / 4) * dla::NCOL + 255) / 256), (unsigned)ch.nq);
     dla::build_bmat_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.M, B, k);
@@ -135,7 +146,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     dim3 grid((unsigned)((ch.max_npad + 255) / 256), (unsigned)ch.nq);
     dla::pack_pixels_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[1], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[1], st));
   if (ch.all_ident && num_lines == 3 && !c->force_pixel_lane_k1) {
     const int sb_per_cta = c->k1_sb_per_cta;
     const int nsbg = (nsb + sb_per_cta - 1) / sb_per_cta;
@@ -154,7 +165,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
         in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pidx, in.pix4, W, U, aux,
         num_lines, raw_stride);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[2], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[2], st));
   if (!c->force_tile_k2) {
     const int64_t ntiles = (int64_t)ch.nq * nsb;
     const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
@@ -165,23 +176,42 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     dla::contract_chol_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K2_THREADS, smem, st>>>(
         in.desc, ch.q0, nsb, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[3], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[3], st));
   if (S > 0 && ll_dla) {
     dla::reduce_kernel<<<(unsigned)ch.nq, 256, 0, st>>>(in.desc, ch.q0, S, sample_ll_chunk, ll_no, ll_dla, lp_no,
                                                          lp_dla, post, map_index);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(c->ev[4], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[4], st));
   CU_TRY(c, cudaGetLastError());
-  if (time_it) {
-    CU_TRY(c, cudaEventSynchronize(c->ev[4]));
-    float ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[1])); c->timing.ms_phi += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[1], c->ev[2])); c->timing.ms_voigt += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[2], c->ev[3])); c->timing.ms_contract += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[3], c->ev[4])); c->timing.ms_reduce += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[4])); c->timing.ms_total += ms;
-  }
   c->timing.launches += (S > 0 && ll_dla) ? 5 : 4;
+  return DLA_OK;
+}
+
+// after the stream has been synchronised: per-kernel device times summed over the chunks
+static int collect_timing(dla_ctx* c, size_t nchunks) {
+  for (size_t i = 0; i < nchunks; ++i) {
+    cudaEvent_t* e = &c->ev_time[5 * i];
+    float ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[0], e[1])); c->timing.ms_phi += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[1], e[2])); c->timing.ms_voigt += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[2], e[3])); c->timing.ms_contract += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[3], e[4])); c->timing.ms_reduce += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[0], e[4])); c->timing.ms_total += ms;
+  }
+  return DLA_OK;
+}
+
+static int ensure_events(dla_ctx* c, size_t nchunks) {
+  while (c->ev_time.size() < 5 * nchunks) {
+    cudaEvent_t e;
+    CU_TRY(c, cudaEventCreate(&e));
+    c->ev_time.push_back(e);
+  }
+  while (c->ev_sync.size() < 2 * nchunks) {
+    cudaEvent_t e;
+    CU_TRY(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    c->ev_sync.push_back(e);
+  }
   return DLA_OK;
 }
 
@@ -264,6 +294,8 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
   } while (0)
   CREATE_TRY(cudaSetDevice(device));
   CREATE_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CREATE_TRY(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+  CREATE_TRY(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
   for (auto& ev : c->ev) CREATE_TRY(cudaEventCreate(&ev));
   // per-line constants, computed as libcerf's voigt() does: (x + i gamma)/sqrt(2)/sigma, /sqrt(2 pi)/sigma
   {
@@ -351,6 +383,10 @@ void dla_destroy(dla_ctx* c) {
     b->release();
   for (auto& ev : c->ev)
     if (ev) cudaEventDestroy(ev);
+  for (auto& ev : c->ev_time) cudaEventDestroy(ev);
+  for (auto& ev : c->ev_sync) cudaEventDestroy(ev);
+  if (c->s_in) cudaStreamDestroy(c->s_in);
+  if (c->s_out) cudaStreamDestroy(c->s_out);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -389,12 +425,12 @@ int dla_set_samples(dla_ctx* c, const double* offset_samples, const double* nhi_
   return DLA_OK;
 }
 
-int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
-                    const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
-                    const double* mu, const double* omega2, const double* noise_variance, const double* M,
-                    const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
-                    const double* log_prior_no_dla) {
-  if (!c) return DLA_ERR_BAD_ARG;
+// Validation, per-quasar descriptors, chunk plan and device buffers for a batch.  No copies yet.
+static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
+                      const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
+                      const double* mu, const double* omega2, const double* noise_variance, const double* M,
+                      const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
+                      const double* log_prior_no_dla) {
   c->staged = false;
   c->ran = false;
   if (Q < 0 || Q > (int64_t)INT32_MAX) BAD_ARG(c, "dla_stage_batch: Q out of range");
@@ -408,7 +444,6 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
   CU_TRY(c, cudaSetDevice(c->device));
   const int64_t S = c->p.num_samples;
   const int64_t S_pad = round_up(S + 1, dla::TS);
-  // descriptors + validation
   c->h_desc.assign((size_t)Q, QuasarDesc{});
   for (int64_t q = 0; q < Q; ++q) {
     const int64_t n = pix_ptr[q + 1] - pix_ptr[q], P = pad_ptr[q + 1] - pad_ptr[q];
@@ -432,13 +467,15 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
     }
     d.ident = ident ? 1 : 0;
   }
-  // chunk plan: split so that W+U of a chunk fit the workspace budget, chunks balanced
+  // chunk plan: W+U of a chunk fit the workspace budget; at least a few chunks when the batch is
+  // large enough, so that copies of one chunk overlap the kernels of another (dla_eval_batch)
   c->chunks.clear();
   {
     long double total = 0;
     for (int64_t q = 0; q < Q; ++q) total += 16.0L * S_pad * c->h_desc[(size_t)q].npad;
     const int64_t budget = c->p.workspace_bytes;
-    const int64_t nch = std::max<int64_t>(1, (int64_t)ceill(total / budget));
+    const int64_t pipe = std::min<int64_t>(4, Q / 8);
+    const int64_t nch = std::max<int64_t>(std::max<int64_t>(1, pipe), (int64_t)ceill(total / budget));
     const long double target = total / nch;
     int64_t q = 0;
     while (q < Q) {
@@ -446,8 +483,8 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
       long double acc = 0;
       while (q < Q) {
         QuasarDesc& d = c->h_desc[(size_t)q];
-        const long double b = 16.0L * S_pad * d.npad;
-        if (ch.nq > 0 && (acc + b > budget || acc >= target)) break;
+        const long double bts = 16.0L * S_pad * d.npad;
+        if (ch.nq > 0 && (acc + bts > budget || acc >= target)) break;
         d.wu_off = ch.wu_doubles;
         d.bmat_off = ch.bmat_doubles;
         ch.wu_doubles += S_pad * d.npad;
@@ -455,7 +492,7 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
         ch.max_npad = std::max(ch.max_npad, (int)d.npad);
         ch.max_P = std::max(ch.max_P, (int)d.P);
         ch.all_ident = ch.all_ident && d.ident != 0;
-        acc += b;
+        acc += bts;
         ++ch.nq;
         ++q;
       }
@@ -464,34 +501,24 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
   }
   const int64_t npix = pix_ptr[Q], npadtot = pad_ptr[Q];
   const int k = c->p.k;
-  c->timing = dla_timing{};
-  CU_TRY(c, cudaEventRecord(c->ev[5], c->stream));
-  auto up = [&](DevBuf& b, const void* src, size_t bytes) -> cudaError_t {
-    cudaError_t e = b.ensure(std::max<size_t>(bytes, 16));
-    if (e != cudaSuccess || bytes == 0) return e;
-    c->timing.h2d_bytes += (int64_t)bytes;
-    return cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->stream);
-  };
-  CU_TRY(c, up(c->d_desc, c->h_desc.data(), (size_t)Q * sizeof(QuasarDesc)));
-  CU_TRY(c, up(c->d_padded, padded_wavelengths, (size_t)npadtot * 8));
-  CU_TRY(c, up(c->d_pidx, profile_index, (size_t)npix * 4));
-  CU_TRY(c, c->d_pix4.ensure(std::max<size_t>((size_t)npix * 32, 32)));
-  CU_TRY(c, up(c->d_flux, flux, (size_t)npix * 8));
-  CU_TRY(c, up(c->d_mu, mu, (size_t)npix * 8));
-  CU_TRY(c, up(c->d_om, omega2, (size_t)npix * 8));
-  CU_TRY(c, up(c->d_nv, noise_variance, (size_t)npix * 8));
-  CU_TRY(c, up(c->d_M, M, (size_t)npix * k * 8));
-  CU_TRY(c, cudaEventRecord(c->ev[6], c->stream));
-  // outputs
+  auto need = [&](DevBuf& b, size_t bytes) { return b.ensure(std::max<size_t>(bytes, 32)); };
+  CU_TRY(c, need(c->d_desc, (size_t)Q * sizeof(QuasarDesc)));
+  CU_TRY(c, need(c->d_padded, (size_t)npadtot * 8));
+  CU_TRY(c, need(c->d_pidx, (size_t)npix * 4));
+  CU_TRY(c, need(c->d_pix4, (size_t)npix * 32));
+  CU_TRY(c, need(c->d_flux, (size_t)npix * 8));
+  CU_TRY(c, need(c->d_mu, (size_t)npix * 8));
+  CU_TRY(c, need(c->d_om, (size_t)npix * 8));
+  CU_TRY(c, need(c->d_nv, (size_t)npix * 8));
+  CU_TRY(c, need(c->d_M, (size_t)npix * k * 8));
   const size_t q8 = (size_t)std::max<int64_t>(Q, 1) * 8;
-  if (c->p.store_sample_ll) CU_TRY(c, c->d_sample_ll.ensure(std::max<size_t>((size_t)Q * S * 8, 16)));
+  if (c->p.store_sample_ll) CU_TRY(c, need(c->d_sample_ll, (size_t)Q * S * 8));
   CU_TRY(c, c->d_ll_no.ensure(q8));
   CU_TRY(c, c->d_ll_dla.ensure(q8));
   CU_TRY(c, c->d_lp_no.ensure(q8));
   CU_TRY(c, c->d_lp_dla.ensure(q8));
   CU_TRY(c, c->d_post.ensure(2 * q8));
   CU_TRY(c, c->d_map.ensure(q8));
-  // workspace for the largest chunk
   {
     int64_t wu = 0, bm = 0;
     int nq = 0;
@@ -503,13 +530,76 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
     int rc = ensure_workspace(c, std::max<int64_t>(wu, 2), std::max<int64_t>(bm, 2), std::max(nq, 1), S, !c->p.store_sample_ll);
     if (rc != DLA_OK) return rc;
   }
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
-  {
-    float ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]));
-    c->timing.ms_h2d = ms;
-  }
+  int rc = ensure_events(c, std::max<size_t>(1, c->chunks.size()));
+  if (rc != DLA_OK) return rc;
+  c->hin = {pix_ptr, pad_ptr, padded_wavelengths, flux, mu, omega2, noise_variance, M, profile_index};
   c->Q = Q;
+  c->timing = dla_timing{};
+  return DLA_OK;
+}
+
+// H2D of the inputs of chunk i on stream st (chunk 0 also carries the descriptors of the whole
+// batch); records the chunk's "inputs resident" event.
+static int upload_chunk(dla_ctx* c, size_t i, cudaStream_t st) {
+  const Chunk& ch = c->chunks[i];
+  const auto& h = c->hin;
+  const int k = c->p.k;
+  auto up = [&](DevBuf& b, const void* src, size_t off_bytes, size_t bytes) -> cudaError_t {
+    if (bytes == 0) return cudaSuccess;
+    c->timing.h2d_bytes += (int64_t)bytes;
+    return cudaMemcpyAsync((char*)b.p + off_bytes, (const char*)src + off_bytes, bytes, cudaMemcpyHostToDevice, st);
+  };
+  if (i == 0) CU_TRY(c, up(c->d_desc, c->h_desc.data(), 0, (size_t)c->Q * sizeof(QuasarDesc)));
+  const int64_t p0 = h.pix_ptr[ch.q0], p1 = h.pix_ptr[ch.q0 + ch.nq];
+  const int64_t w0 = h.pad_ptr[ch.q0], w1 = h.pad_ptr[ch.q0 + ch.nq];
+  CU_TRY(c, up(c->d_padded, h.padded, (size_t)w0 * 8, (size_t)(w1 - w0) * 8));
+  CU_TRY(c, up(c->d_pidx, h.pidx, (size_t)p0 * 4, (size_t)(p1 - p0) * 4));
+  CU_TRY(c, up(c->d_flux, h.flux, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
+  CU_TRY(c, up(c->d_mu, h.mu, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
+  CU_TRY(c, up(c->d_om, h.om, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
+  CU_TRY(c, up(c->d_nv, h.nv, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
+  CU_TRY(c, up(c->d_M, h.M, (size_t)p0 * k * 8, (size_t)(p1 - p0) * k * 8));
+  CU_TRY(c, cudaEventRecord(c->ev_sync[2 * i], st));
+  return DLA_OK;
+}
+
+// kernels of chunk i on the compute stream, after its inputs are resident
+static int run_chunk(dla_ctx* c, size_t i) {
+  const Chunk& ch = c->chunks[i];
+  const int64_t S = c->p.num_samples;
+  Inputs in{c->d_desc.as<QuasarDesc>(), c->d_padded.as<double>(), c->d_flux.as<double>(), c->d_mu.as<double>(),
+            c->d_om.as<double>(), c->d_nv.as<double>(), c->d_M.as<double>(), c->d_pidx.as<int32_t>(),
+            c->d_pix4.as<double2>()};
+  CU_TRY(c, cudaStreamWaitEvent(c->stream, c->ev_sync[2 * i], 0));
+  double* ll_chunk = c->p.store_sample_ll ? c->d_sample_ll.as<double>() + (int64_t)ch.q0 * S : c->d_ll_chunk.as<double>();
+  int rc = launch_chunk(c, in, ch, S, c->p.k, c->p.num_lines, c->d_offset.as<double>(), c->d_nhi.as<double>(),
+                        c->d_perm.as<int32_t>(), ll_chunk, c->d_ll_no.as<double>(), c->d_ll_dla.as<double>(),
+                        c->d_lp_no.as<double>(), c->d_lp_dla.as<double>(), c->d_post.as<double>(),
+                        c->d_map.as<int32_t>(), &c->ev_time[5 * i]);
+  if (rc != DLA_OK) return rc;
+  CU_TRY(c, cudaEventRecord(c->ev_sync[2 * i + 1], c->stream));
+  c->timing.chunks++;
+  return DLA_OK;
+}
+
+int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
+                    const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
+                    const double* mu, const double* omega2, const double* noise_variance, const double* M,
+                    const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
+                    const double* log_prior_no_dla) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  int rc = plan_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M,
+                      min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
+  if (rc != DLA_OK) return rc;
+  CU_TRY(c, cudaEventRecord(c->ev[5], c->s_in));
+  for (size_t i = 0; i < c->chunks.size(); ++i)
+    if ((rc = upload_chunk(c, i, c->s_in)) != DLA_OK) return rc;
+  CU_TRY(c, cudaEventRecord(c->ev[6], c->s_in));
+  CU_TRY(c, cudaStreamSynchronize(c->s_in));
+  c->hin = {};
+  float ms;
+  CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]));
+  c->timing.ms_h2d = ms;
   c->staged = true;
   return DLA_OK;
 }
@@ -521,26 +611,37 @@ int dla_run_staged(dla_ctx* c) {
     return DLA_ERR_STATE;
   }
   CU_TRY(c, cudaSetDevice(c->device));
-  const int64_t S = c->p.num_samples;
   const int64_t keep_h2d = c->timing.h2d_bytes;
   const double keep_ms_h2d = c->timing.ms_h2d;
   c->timing = dla_timing{};
   c->timing.h2d_bytes = keep_h2d;
   c->timing.ms_h2d = keep_ms_h2d;
-  Inputs in{c->d_desc.as<QuasarDesc>(), c->d_padded.as<double>(), c->d_flux.as<double>(), c->d_mu.as<double>(),
-            c->d_om.as<double>(), c->d_nv.as<double>(), c->d_M.as<double>(), c->d_pidx.as<int32_t>(),
-            c->d_pix4.as<double2>()};
-  for (const Chunk& ch : c->chunks) {
-    double* ll_chunk = c->p.store_sample_ll ? c->d_sample_ll.as<double>() + (int64_t)ch.q0 * S : c->d_ll_chunk.as<double>();
-    int rc = launch_chunk(c, in, ch, S, c->p.k, c->p.num_lines, c->d_offset.as<double>(), c->d_nhi.as<double>(),
-                          c->d_perm.as<int32_t>(), ll_chunk,
-                          c->d_ll_no.as<double>(), c->d_ll_dla.as<double>(), c->d_lp_no.as<double>(),
-                          c->d_lp_dla.as<double>(), c->d_post.as<double>(), c->d_map.as<int32_t>(), true);
+  for (size_t i = 0; i < c->chunks.size(); ++i) {
+    int rc = run_chunk(c, i);
     if (rc != DLA_OK) return rc;
-    c->timing.chunks++;
   }
   CU_TRY(c, cudaStreamSynchronize(c->stream));
+  int rc = collect_timing(c, c->chunks.size());
+  if (rc != DLA_OK) return rc;
   c->ran = true;
+  return DLA_OK;
+}
+
+// D2H of the per-quasar outputs (everything except sample_ll) on stream st
+static int download_small(dla_ctx* c, cudaStream_t st, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
+                          double* log_post_dla, double* model_posteriors, int32_t* map_index) {
+  const int64_t Q = c->Q;
+  auto down = [&](void* dst, const DevBuf& b, size_t bytes) -> cudaError_t {
+    if (!dst || bytes == 0) return cudaSuccess;
+    c->timing.d2h_bytes += (int64_t)bytes;
+    return cudaMemcpyAsync(dst, b.p, bytes, cudaMemcpyDeviceToHost, st);
+  };
+  CU_TRY(c, down(ll_no_dla, c->d_ll_no, (size_t)Q * 8));
+  CU_TRY(c, down(ll_dla, c->d_ll_dla, (size_t)Q * 8));
+  CU_TRY(c, down(log_post_no_dla, c->d_lp_no, (size_t)Q * 8));
+  CU_TRY(c, down(log_post_dla, c->d_lp_dla, (size_t)Q * 8));
+  CU_TRY(c, down(model_posteriors, c->d_post, (size_t)Q * 16));
+  CU_TRY(c, down(map_index, c->d_map, (size_t)Q * 4));
   return DLA_OK;
 }
 
@@ -556,18 +657,12 @@ int dla_fetch_staged(dla_ctx* c, double* sample_ll, double* ll_no_dla, double* l
   const int64_t Q = c->Q, S = c->p.num_samples;
   c->timing.d2h_bytes = 0;
   CU_TRY(c, cudaEventRecord(c->ev[5], c->stream));
-  auto down = [&](void* dst, const DevBuf& b, size_t bytes) -> cudaError_t {
-    if (!dst || bytes == 0) return cudaSuccess;
-    c->timing.d2h_bytes += (int64_t)bytes;
-    return cudaMemcpyAsync(dst, b.p, bytes, cudaMemcpyDeviceToHost, c->stream);
-  };
-  CU_TRY(c, down(sample_ll, c->d_sample_ll, (size_t)Q * S * 8));
-  CU_TRY(c, down(ll_no_dla, c->d_ll_no, (size_t)Q * 8));
-  CU_TRY(c, down(ll_dla, c->d_ll_dla, (size_t)Q * 8));
-  CU_TRY(c, down(log_post_no_dla, c->d_lp_no, (size_t)Q * 8));
-  CU_TRY(c, down(log_post_dla, c->d_lp_dla, (size_t)Q * 8));
-  CU_TRY(c, down(model_posteriors, c->d_post, (size_t)Q * 16));
-  CU_TRY(c, down(map_index, c->d_map, (size_t)Q * 4));
+  if (sample_ll && Q * S > 0) {
+    c->timing.d2h_bytes += Q * S * 8;
+    CU_TRY(c, cudaMemcpyAsync(sample_ll, c->d_sample_ll.p, (size_t)Q * S * 8, cudaMemcpyDeviceToHost, c->stream));
+  }
+  int rc = download_small(c, c->stream, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
+  if (rc != DLA_OK) return rc;
   CU_TRY(c, cudaEventRecord(c->ev[6], c->stream));
   CU_TRY(c, cudaStreamSynchronize(c->stream));
   float ms;
@@ -576,18 +671,50 @@ int dla_fetch_staged(dla_ctx* c, double* sample_ll, double* ll_no_dla, double* l
   return DLA_OK;
 }
 
+// One call, pipelined over the chunks: H2D of chunk i+1 (stream s_in) and D2H of chunk i-1's
+// sample log-likelihoods (stream s_out) run under the kernels of chunk i (compute stream).
 int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
                    const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
                    const double* mu, const double* omega2, const double* noise_variance, const double* M,
                    const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
                    const double* log_prior_no_dla, double* sample_ll, double* ll_no_dla, double* ll_dla,
                    double* log_post_no_dla, double* log_post_dla, double* model_posteriors, int32_t* map_index) {
-  int rc = dla_stage_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2,
-                           noise_variance, M, min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (sample_ll && !c->p.store_sample_ll) BAD_ARG(c, "dla_eval_batch: sample_ll requested but store_sample_ll = 0");
+  int rc = plan_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M,
+                      min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
   if (rc != DLA_OK) return rc;
-  rc = dla_run_staged(c);
+  const int64_t S = c->p.num_samples;
+  const size_t nch = c->chunks.size();
+  CU_TRY(c, cudaEventRecord(c->ev[5], c->s_in));
+  for (size_t i = 0; i < nch; ++i)
+    if ((rc = upload_chunk(c, i, c->s_in)) != DLA_OK) return rc;
+  CU_TRY(c, cudaEventRecord(c->ev[6], c->s_in));
+  for (size_t i = 0; i < nch; ++i) {
+    if ((rc = run_chunk(c, i)) != DLA_OK) return rc;
+    const Chunk& ch = c->chunks[i];
+    if (sample_ll && (int64_t)ch.nq * S > 0) {
+      CU_TRY(c, cudaStreamWaitEvent(c->s_out, c->ev_sync[2 * i + 1], 0));
+      const size_t off = (size_t)ch.q0 * S * 8, bytes = (size_t)ch.nq * S * 8;
+      c->timing.d2h_bytes += (int64_t)bytes;
+      CU_TRY(c, cudaMemcpyAsync((char*)sample_ll + off, (const char*)c->d_sample_ll.p + off, bytes,
+                                cudaMemcpyDeviceToHost, c->s_out));
+    }
+  }
+  if (nch > 0) CU_TRY(c, cudaStreamWaitEvent(c->s_out, c->ev_sync[2 * (nch - 1) + 1], 0));
+  rc = download_small(c, c->s_out, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
   if (rc != DLA_OK) return rc;
-  return dla_fetch_staged(c, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
+  CU_TRY(c, cudaStreamSynchronize(c->s_in));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->s_out));
+  c->hin = {};
+  float ms;
+  CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]));
+  c->timing.ms_h2d = ms;  // span of the input copies on their own stream (they overlap the kernels)
+  if ((rc = collect_timing(c, nch)) != DLA_OK) return rc;
+  c->staged = true;
+  c->ran = true;
+  return DLA_OK;
 }
 
 int dla_get_timing(const dla_ctx* c, dla_timing* out) {
@@ -680,7 +807,7 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
             dnv.as<double>(), dM.as<double>(), reinterpret_cast<const int32_t*>(dzero.p), dpix.as<double2>()};
   rc = launch_chunk(c, in, ch, 0, k, 1, dzero.as<double>(), dzero.as<double>(),
                     reinterpret_cast<const int32_t*>(dzero.p), c->d_ll_chunk.as<double>(),
-                    dout.as<double>(), nullptr, nullptr, nullptr, nullptr, nullptr, false);
+                    dout.as<double>(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
   if (rc != DLA_OK) {
     cleanup();
     return rc;

@@ -232,16 +232,23 @@ class DlaContext:
                 _lib.ptr(lpd, d), _lib.ptr(lpn, d)]
         return args, keep
 
-    def _alloc_outputs(self, Q, want_sample_ll=True):
+    def _alloc_outputs(self, Q, want_sample_ll=True, alloc=None):
+        """Result arrays, NaN-initialised as process_qsos.m:74-82.  ``alloc(shape, dtype)`` may supply
+        the memory (e.g. page-locked host buffers, so that the D2H copies run asynchronously)."""
         S = self.num_samples
+
+        def full(shape, fill, dtype=np.float64):
+            a = np.empty(shape, dtype=dtype) if alloc is None else alloc(shape, dtype)
+            a[...] = fill
+            return a
         out = {
-            "sample_log_likelihoods_dla": (np.full((Q, S), np.nan) if (self.store_sample_ll and want_sample_ll) else None),
-            "log_likelihoods_no_dla": np.full(Q, np.nan),
-            "log_likelihoods_dla": np.full(Q, np.nan),
-            "log_posteriors_no_dla": np.full(Q, np.nan),
-            "log_posteriors_dla": np.full(Q, np.nan),
-            "model_posteriors": np.full((Q, 2), np.nan),
-            "map_ind": np.full(Q, -1, dtype=np.int32),
+            "sample_log_likelihoods_dla": (full((Q, S), np.nan) if (self.store_sample_ll and want_sample_ll) else None),
+            "log_likelihoods_no_dla": full(Q, np.nan),
+            "log_likelihoods_dla": full(Q, np.nan),
+            "log_posteriors_no_dla": full(Q, np.nan),
+            "log_posteriors_dla": full(Q, np.nan),
+            "model_posteriors": full((Q, 2), np.nan),
+            "map_ind": full(Q, -1, np.int32),
         }
         d = C.c_double
         args = [_lib.ptr(out["sample_log_likelihoods_dla"], d), _lib.ptr(out["log_likelihoods_no_dla"], d),
