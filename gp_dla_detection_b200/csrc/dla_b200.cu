@@ -91,7 +91,7 @@ struct dla_ctx {
   DevBuf d_desc, d_padded, d_pidx, d_flux, d_mu, d_om, d_nv, d_M, d_pix4;
   DevBuf d_sample_ll, d_ll_no, d_ll_dla, d_lp_no, d_lp_dla, d_post, d_map;
   // chunk workspace
-  DevBuf d_W, d_U, d_bmat, d_aux, d_ll_chunk;
+  DevBuf d_W, d_U, d_bmat, d_aux, d_ll_chunk, d_G;
   dla_timing timing{};
 };
 
@@ -118,6 +118,22 @@ static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * 
 // ------------------------------------------------------------------------------------------
 // chunk execution
 // ------------------------------------------------------------------------------------------
+// Column geometry of the contraction: the fused path (k <= 20) has NCOL = 240 columns in one CTA
+// tile; the generic-rank path splits roundup(T,8) + roundup(k,8) columns into column blocks.
+struct ColGeom {
+  bool generic;
+  int ncol, voff, nblocks, tpw;
+};
+static ColGeom col_geom(int k) {
+  if (k <= dla::KMAX) return {false, dla::NCOL, dla::VOFF, 1, dla::NT / 2};
+  const int T8 = (int)round_up((int64_t)k * (k + 1) / 2, 8);
+  const int ncol = T8 + (int)round_up(k, 8);
+  const int ntile = ncol / 8;
+  const int nblocks = (ntile + dla::NT - 1) / dla::NT;
+  const int tpw = (ntile + 2 * nblocks - 1) / (2 * nblocks);
+  return {true, ncol, T8, nblocks, tpw};
+}
+
 static int k1_warps_for(int raw_stride) {
   const size_t budget = 200 * 1024 - 256;
   int w = (int)(budget / ((size_t)raw_stride * 8));
@@ -132,6 +148,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
                         cudaEvent_t* tev /* 5 timing events or nullptr */) {
   const bool time_it = tev != nullptr;
   const int nsb = (int)((S + 1 + dla::TS - 1) / dla::TS);
+  const ColGeom gen = col_geom(k);
   double* W = c->d_W.as<double>();
   double* U = c->d_U.as<double>();
   double* B = c->d_bmat.as<double>();
@@ -139,8 +156,8 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   cudaStream_t st = c->stream;
   if (time_it) CU_TRY(c, cudaEventRecord(tev[0], st));
   {
-    dim3 grid((unsigned)(((int64_t)(ch.max_npad / 4) * dla::NCOL + 255) / 256), (unsigned)ch.nq);
-    dla::build_bmat_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.M, B, k);
+    dim3 grid((unsigned)(((int64_t)(ch.max_npad / 4) * gen.ncol + 255) / 256), (unsigned)ch.nq);
+    dla::build_bmat_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.M, B, k, gen.ncol, gen.voff);
   }
   {
     dim3 grid((unsigned)((ch.max_npad + 255) / 256), (unsigned)ch.nq);
@@ -166,7 +183,16 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
         num_lines, raw_stride);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[2], st));
-  if (!c->force_tile_k2) {
+  if (gen.generic) {
+    const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
+    dim3 grid((unsigned)((int64_t)ch.nq * nsb), (unsigned)gen.nblocks);
+    dla::contract_block_kernel<<<grid, dla::K2_THREADS, smem, st>>>(in.desc, ch.q0, nsb, W, U, B, c->d_G.as<double>(),
+                                                                     gen.ncol, gen.voff / 8, gen.tpw);
+    dim3 g2((unsigned)((S + 1 + dla::CHG_WARPS - 1) / dla::CHG_WARPS), (unsigned)ch.nq);
+    const size_t sm2 = (size_t)dla::CHG_WARPS * (k + 1) * (k + 2) * 8;
+    dla::chol_generic_kernel<<<g2, dla::CHG_WARPS * 32, sm2, st>>>(in.desc, ch.q0, nsb, S, c->d_G.as<double>(), aux,
+                                                                    d_perm, sample_ll_chunk, ll_no, k, gen.ncol, gen.voff);
+  } else if (!c->force_tile_k2) {
     const int64_t ntiles = (int64_t)ch.nq * nsb;
     const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
     dla::contract_chol_persistent_kernel<<<grid, dla::K2P_THREADS, dla::K2P_SMEM_BYTES, st>>>(
@@ -183,7 +209,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[4], st));
   CU_TRY(c, cudaGetLastError());
-  c->timing.launches += (S > 0 && ll_dla) ? 5 : 4;
+  c->timing.launches += ((S > 0 && ll_dla) ? 5 : 4) + (gen.generic ? 1 : 0);
   return DLA_OK;
 }
 
@@ -215,12 +241,14 @@ static int ensure_events(dla_ctx* c, size_t nchunks) {
   return DLA_OK;
 }
 
-static int ensure_workspace(dla_ctx* c, int64_t wu_doubles, int64_t bmat_doubles, int nq, int64_t S, bool need_ll_chunk) {
+static int ensure_workspace(dla_ctx* c, int k, int64_t wu_doubles, int64_t bmat_doubles, int nq, int64_t S, bool need_ll_chunk) {
   const int64_t S_pad = round_up(S + 1, dla::TS);
   CU_TRY(c, c->d_W.ensure((size_t)wu_doubles * 8));
   CU_TRY(c, c->d_U.ensure((size_t)wu_doubles * 8));
-  CU_TRY(c, c->d_bmat.ensure((size_t)bmat_doubles * 8));
+  const ColGeom gen = col_geom(k);
+  CU_TRY(c, c->d_bmat.ensure((size_t)(bmat_doubles / dla::NCOL + 1) * gen.ncol * 8));
   CU_TRY(c, c->d_aux.ensure((size_t)nq * 2 * S_pad * 8));
+  if (gen.generic) CU_TRY(c, c->d_G.ensure((size_t)nq * S_pad * gen.ncol * 8));
   if (need_ll_chunk) CU_TRY(c, c->d_ll_chunk.ensure((size_t)std::max<int64_t>(1, (int64_t)nq * S) * 8));
   return DLA_OK;
 }
@@ -249,8 +277,8 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     return DLA_ERR_BAD_ARG;
   }
   *out = nullptr;
-  if (p->k < 1 || p->k > dla::KMAX) {
-    g_create_error = "dla_create: k must be in 1..20 (fused DMMA path)";
+  if (p->k < 1 || p->k > dla::KGEN_MAX) {
+    g_create_error = "dla_create: k must be in 1..64 (1..20 fused epilogue, 21..64 column-block path)";
     return DLA_ERR_BAD_ARG;
   }
   if (p->num_lines < 1 || p->num_lines > DLA_MAX_LINES) {
@@ -366,6 +394,10 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)dla::K2P_SMEM_BYTES));
+  CREATE_TRY(cudaFuncSetAttribute(dla::contract_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
+  CREATE_TRY(cudaFuncSetAttribute(dla::chol_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  dla::CHG_WARPS * (dla::KGEN_MAX + 1) * (dla::KGEN_MAX + 2) * 8));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #undef CREATE_TRY
@@ -379,7 +411,7 @@ void dla_destroy(dla_ctx* c) {
   cudaStreamSynchronize(c->stream);
   for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_perm, &c->d_etab256, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
                     &c->d_nv, &c->d_M, &c->d_pix4, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
-                    &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk})
+                    &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk, &c->d_G})
     b->release();
   for (auto& ev : c->ev)
     if (ev) cudaEventDestroy(ev);
@@ -472,7 +504,8 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
   c->chunks.clear();
   {
     long double total = 0;
-    for (int64_t q = 0; q < Q; ++q) total += 16.0L * S_pad * c->h_desc[(size_t)q].npad;
+    const long double gq = col_geom(c->p.k).generic ? 8.0L * S_pad * col_geom(c->p.k).ncol : 0.0L;  // G rows
+    for (int64_t q = 0; q < Q; ++q) total += 16.0L * S_pad * c->h_desc[(size_t)q].npad + gq;
     const int64_t budget = c->p.workspace_bytes;
     const int64_t pipe = std::min<int64_t>(4, Q / 8);
     const int64_t nch = std::max<int64_t>(std::max<int64_t>(1, pipe), (int64_t)ceill(total / budget));
@@ -483,7 +516,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
       long double acc = 0;
       while (q < Q) {
         QuasarDesc& d = c->h_desc[(size_t)q];
-        const long double bts = 16.0L * S_pad * d.npad;
+        const long double bts = 16.0L * S_pad * d.npad + gq;
         if (ch.nq > 0 && (acc + bts > budget || acc >= target)) break;
         d.wu_off = ch.wu_doubles;
         d.bmat_off = ch.bmat_doubles;
@@ -527,7 +560,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
       bm = std::max(bm, ch.bmat_doubles);
       nq = std::max(nq, ch.nq);
     }
-    int rc = ensure_workspace(c, std::max<int64_t>(wu, 2), std::max<int64_t>(bm, 2), std::max(nq, 1), S, !c->p.store_sample_ll);
+    int rc = ensure_workspace(c, c->p.k, std::max<int64_t>(wu, 2), std::max<int64_t>(bm, 2), std::max(nq, 1), S, !c->p.store_sample_ll);
     if (rc != DLA_OK) return rc;
   }
   int rc = ensure_events(c, std::max<size_t>(1, c->chunks.size()));
@@ -761,7 +794,7 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
   if (!c) return DLA_ERR_BAD_ARG;
   if (!y || !mu || !M || !d || !log_p) BAD_ARG(c, "dla_log_mvnpdf_low_rank: NULL pointer");
   if (n < 1 || n > (1 << 24)) BAD_ARG(c, "dla_log_mvnpdf_low_rank: n out of range");
-  if (k < 1 || k > dla::KMAX) BAD_ARG(c, "dla_log_mvnpdf_low_rank: k must be in 1..20");
+  if (k < 1 || k > dla::KGEN_MAX) BAD_ARG(c, "dla_log_mvnpdf_low_rank: k must be in 1..64");
   CU_TRY(c, cudaSetDevice(c->device));
   c->staged = false;  // reuses the chunk workspace
   c->ran = false;
@@ -773,7 +806,7 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
   hd.npad = (int32_t)round_up(n, dla::KC);
   hd.ident = 1;
   Chunk ch{0, 1, (int64_t)dla::TS * hd.npad, (int64_t)hd.npad * dla::NCOL, hd.npad, hd.P, false};
-  int rc = ensure_workspace(c, ch.wu_doubles, ch.bmat_doubles, 1, 0, true);
+  int rc = ensure_workspace(c, k, ch.wu_doubles, ch.bmat_doubles, 1, 0, true);
   if (rc != DLA_OK) return rc;
   DevBuf dd, dy, dmu, dM, dzero, dnv, dout, dpix;
   std::vector<double> zeros((size_t)n, 0.0);

@@ -88,21 +88,23 @@ struct QuasarDesc {
 // K0: Bmat[pc][col][kk] for pixel p = 4*pc + kk:
 //   col = i(i+1)/2 + l (l <= i < k): M[p,i]*M[p,l];  col = VOFF + i: M[p,i];  else 0;  p >= n: 0.
 // ----------------------------------------------------------------------------------------------
+// ncol / voff are NCOL / VOFF on the fused k <= 20 path; the generic-rank path passes its own
+// (bmat_off of the descriptor is in units of npad * NCOL doubles and is rescaled by ncol / NCOL).
 __global__ void build_bmat_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ M,
-                                  double* __restrict__ bmat, int k) {
+                                  double* __restrict__ bmat, int k, int ncol, int voff) {
   const QuasarDesc d = desc[q0 + blockIdx.y];
   const int npc = d.npad / 4;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;  // (pc, col)
-  if (idx >= npc * NCOL) return;
-  const int pc = idx / NCOL, col = idx % NCOL;
+  if (idx >= npc * ncol) return;
+  const int pc = idx / ncol, col = idx % ncol;
   int i = -1, l = -1;
   if (col < k * (k + 1) / 2) {
     i = (int)((sqrt(8.0 * col + 1.0) - 1.0) * 0.5);
     while (i * (i + 1) / 2 > col) --i;
     while ((i + 1) * (i + 2) / 2 <= col) ++i;
     l = col - i * (i + 1) / 2;
-  } else if (col >= VOFF && col < VOFF + k) {
-    i = col - VOFF;
+  } else if (col >= voff && col < voff + k) {
+    i = col - voff;
   }
   const double* Mq = M + (int64_t)k * d.pix_off;  // column-major n x k
   double out[4];
@@ -116,7 +118,7 @@ __global__ void build_bmat_kernel(const QuasarDesc* __restrict__ desc, int q0, c
     }
     out[kk] = v;
   }
-  double* dst = bmat + d.bmat_off + ((int64_t)pc * NCOL + col) * 4;
+  double* dst = bmat + d.bmat_off / NCOL * ncol + ((int64_t)pc * ncol + col) * 4;
   reinterpret_cast<double2*>(dst)[0] = make_double2(out[0], out[1]);
   reinterpret_cast<double2*>(dst)[1] = make_double2(out[2], out[3]);
 }
@@ -1127,6 +1129,161 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
         else if (s == S) ll_no_dla[q0 + ql] = lp;
       }
     }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Generic-rank path (20 < k <= KGEN_MAX; BASELINE config 5 is k = 40 on 2433 pixels).
+// The accumulator tile of one sample block no longer fits the register file (k = 40: 860 columns),
+// so the contraction runs per COLUMN BLOCK of <= 30 eight-column tiles: grid = (tiles, column
+// blocks), every block re-reads W/U (27 flop/B at k = 40, far above the FP64 ridge) and writes its
+// slice of G = [W.Phi | U.M] to HBM; a second kernel does the (k+1) x (k+1) bordered Cholesky per
+// sample in shared memory, one warp per sample.
+//   columns: [0, T) vech(B - I), zero padding to T8 = roundup(T, 8), [T8, T8 + k) v, padding to ncol.
+// ----------------------------------------------------------------------------------------------
+constexpr int KGEN_MAX = 64;
+
+__global__ void __launch_bounds__(K2_THREADS, 1)
+contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, const double* __restrict__ Wbuf,
+                      const double* __restrict__ Ubuf, const double* __restrict__ bmat,
+                      double* __restrict__ Gbuf /* [nq][S_pad][ncol] */, int ncol, int vtile /* first U tile */,
+                      int tpw /* active tiles per warp, <= 15 */) {
+  extern __shared__ __align__(128) unsigned char k2_smem_raw[];
+  double* smem = reinterpret_cast<double*>(k2_smem_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)K2_STAGES * STAGE_DOUBLES);
+  const int ql = blockIdx.x / nsb, sb = blockIdx.x % nsb, cb = blockIdx.y;
+  const QuasarDesc d = desc[q0 + ql];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int npc = d.npad >> 2;
+  const int nchunks = d.npad / KC;
+  const int ntile_total = ncol >> 3;
+  const int tile0 = cb * 2 * tpw;                       // first tile of this column block
+  const int ntb = min(2 * tpw, ntile_total - tile0);    // tiles in this block
+  const double* Wsrc = Wbuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
+  const double* Usrc = Ubuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
+  const double* Bsrc = bmat + d.bmat_off / NCOL * ncol + (int64_t)tile0 * 32;
+
+  if (tid == 0) {
+    for (int s = 0; s < K2_STAGES; ++s) mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const uint32_t bbytes = (uint32_t)ntb * 32 * 8;  // one pixel quad of this block's B columns
+  auto issue = [&](int c) {
+    const int st = c % K2_STAGES;
+    double* dst = smem + (size_t)st * STAGE_DOUBLES;
+    mbar_expect_tx(&full[st], 2 * STAGE_W_DOUBLES * 8 + (KC / 4) * bbytes);
+    bulk_g2s(dst, Wsrc + (int64_t)c * STAGE_W_DOUBLES, STAGE_W_DOUBLES * 8, &full[st]);
+    bulk_g2s(dst + STAGE_W_DOUBLES, Usrc + (int64_t)c * STAGE_W_DOUBLES, STAGE_W_DOUBLES * 8, &full[st]);
+#pragma unroll
+    for (int kc = 0; kc < KC / 4; ++kc)
+      bulk_g2s(dst + 2 * STAGE_W_DOUBLES + kc * (NCOL * 4), Bsrc + ((int64_t)c * (KC / 4) + kc) * ncol * 4, bbytes,
+               &full[st]);
+  };
+  if (tid == 0) {
+    const int pre = nchunks < K2_STAGES ? nchunks : K2_STAGES;
+    for (int c = 0; c < pre; ++c) issue(c);
+  }
+  const int mrow = warp & 3, half = warp >> 2;
+  constexpr int TPW = NT / 2;
+  double acc[TPW][4];
+#pragma unroll
+  for (int j = 0; j < TPW; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0;
+  const int wt0 = half * tpw;                 // this warp's first tile within the block
+  const int nact = max(0, min(tpw, ntb - wt0));
+
+  for (int c = 0; c < nchunks; ++c) {
+    const int st = c % K2_STAGES;
+    mbar_wait(&full[st], (uint32_t)((c / K2_STAGES) & 1));
+    const double* Ws = smem + (size_t)st * STAGE_DOUBLES;
+    const double* Us = Ws + STAGE_W_DOUBLES;
+    const double* Bs = Us + STAGE_W_DOUBLES;
+#pragma unroll
+    for (int kc = 0; kc < KC / 4; ++kc) {
+      const double aw0 = Ws[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+      const double aw1 = Ws[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+      const double au0 = Us[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+      const double au1 = Us[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+      const double* bp = Bs + kc * (NCOL * 4) + wt0 * 32 + lane;
+#pragma unroll
+      for (int j = 0; j < TPW; ++j) {
+        if (j < nact) {  // warp-uniform
+          const double b = bp[j * 32];
+          const bool isv = (tile0 + wt0 + j) >= vtile;
+          dmma884(acc[j][0], acc[j][1], isv ? au0 : aw0, b);
+          dmma884(acc[j][2], acc[j][3], isv ? au1 : aw1, b);
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && c + K2_STAGES < nchunks) issue(c + K2_STAGES);
+  }
+  // this block's slice of G, straight from the accumulator fragments (16-byte stores)
+  {
+    const int64_t S_pad = (int64_t)nsb * TS;
+    const int r0 = (2 * mrow) * 8 + (lane >> 2);
+    double* g0 = Gbuf + ((int64_t)ql * S_pad + (int64_t)sb * TS + r0) * ncol + (tile0 + wt0) * 8 + 2 * (lane & 3);
+#pragma unroll
+    for (int j = 0; j < TPW; ++j) {
+      if (j < nact) {
+        *reinterpret_cast<double2*>(g0 + j * 8) = make_double2(acc[j][0], acc[j][1]);
+        *reinterpret_cast<double2*>(g0 + (int64_t)8 * ncol + j * 8) = make_double2(acc[j][2], acc[j][3]);
+      }
+    }
+  }
+}
+
+// One warp per sample: bordered matrix [[I + G, v], [v^T, q0]] in shared memory (row stride k + 2),
+// right-looking Cholesky over the first k columns; the corner ends as q0 - t^T t and the product of
+// the pivots (kept in [1,2) with an integer exponent) gives log|B| (log_mvnpdf_low_rank.m:23-32).
+constexpr int CHG_WARPS = 4;
+__global__ void __launch_bounds__(CHG_WARPS * 32)
+chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S, const double* __restrict__ Gbuf,
+                    const double* __restrict__ aux, const int32_t* __restrict__ perm, double* __restrict__ sample_ll,
+                    double* __restrict__ ll_no_dla, int k, int ncol, int voff) {
+  extern __shared__ double chg_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ld = k + 2, kb = k + 1;
+  double* A = chg_smem + (size_t)warp * kb * ld;
+  const int64_t S_pad = (int64_t)nsb * TS;
+  const int ql = blockIdx.y;
+  const int64_t s = (int64_t)blockIdx.x * CHG_WARPS + warp;
+  if (s > S) return;  // whole warp
+  const double* row = Gbuf + ((int64_t)ql * S_pad + s) * ncol;
+  const double* auxq = aux + (int64_t)ql * 2 * S_pad;
+  for (int i = 0; i < k; ++i)
+    for (int l = lane; l <= i; l += 32) A[i * ld + l] = row[((i * (i + 1)) >> 1) + l] + (l == i ? 1.0 : 0.0);
+  for (int l = lane; l < k; l += 32) A[k * ld + l] = row[voff + l];
+  if (lane == 0) A[k * ld + k] = auxq[s];
+  __syncwarp();
+  double pprod = 1.0;
+  int esum = 0;
+  for (int j = 0; j < k; ++j) {
+    const double piv = A[j * ld + j];
+    const double inv = rsqrt(piv);
+    {
+      pprod *= piv;
+      const int hi = __double2hiint(pprod);
+      const int e = ((hi >> 20) & 0x7ff) - 1023;
+      if (piv > 0.0 && e > -1000 && e < 1000) {  // renormalise; non-positive / non-finite pivots poison the result as chol would fail
+        esum += e;
+        pprod = __hiloint2double(hi - (e << 20), __double2loint(pprod));
+      }
+    }
+    for (int i = j + 1 + lane; i <= k; i += 32) A[i * ld + j] *= inv;
+    __syncwarp();
+    for (int l = j + 1; l <= k; ++l) {
+      const double Llj = A[l * ld + j];
+      for (int i = l + lane; i <= k; i += 32) A[i * ld + l] = fma(-A[i * ld + j], Llj, A[i * ld + l]);
+    }
+    __syncwarp();
+  }
+  if (lane == 0) {
+    const double qq = A[k * ld + k];
+    const double logdet = fma((double)esum, 0.693147180559945309417232, log(pprod));
+    const double lp = -0.5 * (qq + (auxq[S_pad + s] + logdet) + (double)desc[q0 + ql].n * LOG_2PI);
+    if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
+    else ll_no_dla[q0 + ql] = lp;
   }
 }
 

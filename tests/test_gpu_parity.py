@@ -36,7 +36,7 @@ def test_voigt_seam_matches_reference_voigt_c(oracle):
         assert np.max(np.abs(ctx.voigt(p.padded_wavelengths, z, 1e21, None) - ref_fn(p.padded_wavelengths, z, 1e21, 31))) <= 1e-12
 
 
-@pytest.mark.parametrize("n,k", [(64, 1), (97, 5), (256, 20), (1217, 20), (1000, 13)])
+@pytest.mark.parametrize("n,k", [(64, 1), (97, 5), (256, 20), (1217, 20), (1000, 13), (300, 21), (2433, 40), (777, 64)])
 def test_log_mvnpdf_low_rank_seam(oracle, n, k):
     rng = np.random.default_rng(n * 100 + k)
     y, mu = rng.standard_normal(n), rng.standard_normal(n) * 0.1
@@ -64,6 +64,17 @@ def test_config1_subset_parity(oracle):
     ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
     worst = assert_parity(got, ref)
     print("config1 subset worst per-sample rel err", worst)
+
+
+def test_config5_rank40_parity(oracle):
+    """BASELINE config 5 shape (k = 40 null model on the 0.125 A grid, 2433 pixels): the column-block
+    contraction + shared-memory Cholesky path, on a subset the oracle finishes in seconds."""
+    params, model, samples, sp, prepared = prepared_config("config5", 2, 200)
+    assert prepared[0].n == 2433 and prepared[0].M.shape[1] == 40
+    got = _run_gpu(prepared, samples, 40, 200, sp.log_priors_dla, sp.log_priors_no_dla)
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    worst = assert_parity(got, ref)
+    print("config5 subset worst per-sample rel err", worst)
 
 
 @pytest.mark.parametrize("mask_gather", ["reference", "intended"])
