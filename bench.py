@@ -28,6 +28,20 @@ sys.path.insert(0, ROOT)
 
 METRIC = "quasars/sec"
 N_PIX, K_RANK = 1217, 20
+# K2's DRAM traffic per quasar from the committed ncu --set full capture (1.6245 + 0.0045 GB for one
+# 8-quasar launch, profiles/r01_ncu_full_summary.txt); not measured inside bench.py
+NCU_K2_DRAM_GB_PER_QUASAR = (1.624543 + 0.004485) / 8
+# BASELINE.json configs as (rank, grid spacing, ragged masking, hypotheses); SURVEY.md 8(d)
+WORKLOADS = {
+    "config2": {"k": 20, "dlambda": 0.25, "ragged": False, "samples": 10000, "pixels": 1217,
+                "name": "BASELINE config 2 shape (DR12Q-scale synthetic batch)"},
+    "config3": {"k": 20, "dlambda": 0.25, "ragged": True, "samples": 10000, "pixels": 1217,
+                "name": "BASELINE config 3 shape (ragged realistic masking, 200-1217 kept pixels)"},
+    "config4": {"k": 20, "dlambda": 0.25, "ragged": False, "samples": 100000, "pixels": 1217,
+                "name": "BASELINE config 4 shape (dense prior sampling, 100000 hypotheses)"},
+    "config5": {"k": 40, "dlambda": 0.125, "ragged": False, "samples": 10000, "pixels": 2433,
+                "name": "BASELINE config 5 shape (stressed contraction, k=40 on the 0.125 A grid)"},
+}
 
 
 def parse_args():
@@ -37,10 +51,18 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--quasars", type=int, default=192, help="quasars per GPU per step")
-    ap.add_argument("--samples", type=int, default=10000, help="num_dla_samples (config 2: 10000)")
+    ap.add_argument("--samples", type=int, default=None, help="num_dla_samples (config 2: 10000)")
+    ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS),
+                    help="BASELINE.json config shape; config2 is the bench line, the others are side measurements")
     ap.add_argument("--cpu-baseline-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    args = ap.parse_args()
+    global N_PIX, K_RANK
+    w = WORKLOADS[args.workload]
+    K_RANK, N_PIX = w["k"], w["pixels"]
+    if args.samples is None:
+        args.samples = w["samples"]
+    return args
 
 
 # ------------------------------------------------------------------------------------------------
@@ -143,9 +165,10 @@ def make_workload(args, rank):
     from gp_dla_detection_b200.process_qsos import PackedBatch, prepare_quasar
     from gp_dla_detection_b200.set_parameters import Parameters
     params = Parameters(k=K_RANK, num_dla_samples=args.samples)
-    model = synthetic.make_model(K_RANK, 0.25, 20260002, params)
+    w = WORKLOADS[args.workload]
+    model = synthetic.make_model(K_RANK, w["dlambda"], 20260002, params)
     samples = synthetic.make_samples(args.samples, params)
-    sp = synthetic.make_spectra(args.quasars, model, 20260002 + 1000 + rank, False, params)
+    sp = synthetic.make_spectra(args.quasars, model, 20260002 + 1000 + rank, w["ragged"], params)
     prepared = [prepare_quasar(w, f, v, m, z, model, params)
                 for w, f, v, m, z in zip(sp.all_wavelengths, sp.all_flux, sp.all_noise_variance, sp.all_pixel_mask,
                                          sp.z_qsos)]
@@ -153,13 +176,13 @@ def make_workload(args, rank):
 
 
 def config_dict(args, world):
-    return {"workload": f"BASELINE config 2 shape (DR12Q-scale synthetic batch): {N_PIX} px, k={K_RANK}, "
+    return {"workload": f"{WORKLOADS[args.workload]['name']}: {N_PIX} px, k={K_RANK}, "
                         f"S={args.samples} hypotheses/quasar; {args.quasars} quasars per GPU per step, sharded by "
                         f"quasar over {world} GPU(s), no collective; 162861 quasars = "
                         f"{162861 / (args.quasars * world):.0f} such steps",
             "quasars_per_gpu_per_step": args.quasars, "num_dla_samples": args.samples, "pixels": N_PIX, "k": K_RANK,
             "l2": "per-step working set (W,U weight tiles, %.1f GB/GPU) far exceeds the 126 MB L2"
-                  % (args.quasars * 2 * 8 * 10048 * 1232 / 1e9)}
+                  % (args.quasars * 2 * 8 * (args.samples + 64) * (N_PIX + 15) / 1e9)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -295,9 +318,13 @@ def run_ours(args):
     t_contract = ev_ms["ms_contract"] * 1e-3 / args.steps
     t_voigt = ev_ms["ms_voigt"] * 1e-3 / args.steps
     ach = flop_per_step / t_contract / 1e12
-    roofline = {"kernel": "contract_chol_kernel (K2: DMMA contraction + Cholesky epilogue)", "bound": "tensor",
+    k2_name = ("contract_chol_persistent_kernel (K2: persistent DMMA contraction + Cholesky epilogue)" if K_RANK <= 20 else
+               "contract_block_kernel + chol_generic_kernel (K2 generic rank: column-block DMMA contraction, smem Cholesky)")
+    roofline = {"kernel": k2_name, "bound": "tensor",
                 "achieved": ach, "peak": dgemm_tflops, "unit": "TFLOP/s", "frac": ach / dgemm_tflops,
-                "traffic": None,
+                "traffic": (NCU_K2_DRAM_GB_PER_QUASAR * Q / max(1, tm["chunks"])) if args.workload == "config2" and S == 10000 else None,
+                "traffic_unit": "GB per launch (dram__bytes_read.sum + dram__bytes_write.sum of profiles/r01_ncu_full_summary.txt, "
+                                "scaled from its 8-quasar launch; algorithmic W+U bytes are 0.198 GB per quasar)",
                 "peak_source": "FP64 tensor peak = cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json "
                                "has no FP64 figure; the profiling guide states no FP64 fallback)",
                 "algorithmic_flop_per_launch": flop_per_step / max(1, tm["chunks"]),
@@ -310,7 +337,7 @@ def run_ours(args):
                       "faddeeva_evals_per_s": 3.0 * S * float((batch.n_full + 6).sum()) / t_voigt,
                       "ms_per_step": 1e3 * t_voigt,
                       "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"}
-    dominant = "K1 voigt_weights_lane_kernel" if t_voigt > t_contract else "K2 contract_chol_kernel"
+    dominant = "K1 voigt_weights_lane_kernel" if t_voigt > t_contract else "K2 " + k2_name.split(" ")[0]
 
     if rank == 0:
         cpu = None
