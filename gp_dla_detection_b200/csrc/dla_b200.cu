@@ -357,6 +357,8 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     h.k256 = 256.0 * 1.4426950408889634074;
     h.nln2hi256 = -6.93147180369123816490e-01 / 256.0;
     h.nln2lo256 = -1.90821492927058770002e-10 / 256.0;
+    h.nln2_256 = -0.693147180559945309417232 / 256.0;
+    for (int j = 0; j < DLA_MAX_LINES; ++j) h.g1p[j] = h.gq[1] - h.y2T[j];
     h.k32 = 32.0 * 1.4426950408889634074;  // 32 / ln 2
     h.magic = 6755399441055744.0;           // 1.5 * 2^52: adding it rounds to the nearest integer
     h.nln2hi32 = -6.93147180369123816490e-01 / 32.0;  // exact scalings of the hi/lo split of ln 2
@@ -377,6 +379,7 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
       h.hi_near = hi_of(DLA_FADD_XNEAR);
       h.hi_64 = hi_of(64.0);
       h.hi_256 = hi_of(256.0);
+      h.hi_64x = hi_of(64.5);
     }
     CREATE_TRY(cudaMemcpyToSymbol(dla::g_lines, &h, sizeof h));
     double e256[256];

@@ -62,9 +62,11 @@ struct LineConsts {
   double ec[7];
   double etab[32];             // 2^(i/32)
   // high 32 bits of the velocity^2 thresholds for |x| < 16 (core), < 64, < 256 (series length)
-  int hi_near, hi_64, hi_256, pad_;
+  int hi_near, hi_64, hi_256, hi_64x;  // hi_64x: 64.5 widths, so that fma-velocity values never reach the 4-term series below 64
   // exp for the sample-per-lane kernel: t = (256 m + i) ln2/256 + r, |r| <= ln2/512, Taylor degree 4
   double k256, nln2hi256, nln2lo256;
+  double nln2_256;             // -ln2/256 in one constant (|t| <= 707: reduction error <= 8e-14 at the far end)
+  double g1p[DLA_MAX_LINES];   // gq[1] - y2T_j: the O(y^2) correction folded into the s^1 coefficient
 };
 __device__ __constant__ LineConsts g_lines;
 
@@ -511,12 +513,12 @@ constexpr int K1S_THREADS = TS * K1S_NSEG;
 // exp(t), t <= 0, result >= 2^-1020 (t is clamped at -707: a transmission of 1e-307 and one of 0
 // are the same number to every consumer: a^2 underflows either way).  NaN propagates.
 __device__ __forceinline__ double exp_tab256(double t, const double* __restrict__ etab_s) {
-  t = (t < -707.0) ? -707.0 : t;
+  // clamp on the high word (t <= 0 here; a positive NaN compares below the threshold and propagates)
+  if ((unsigned)__double2hiint(t) > 0xC0861800u) t = -707.0;  // hi word of -707.0
   const double kd = fma(t, g_lines.k256, g_lines.magic);
   const int ki = __double2loint(kd);
   const double kf = kd - g_lines.magic;
-  double r = fma(kf, g_lines.nln2hi256, t);
-  r = fma(kf, g_lines.nln2lo256, r);
+  const double r = fma(kf, g_lines.nln2_256, t);
   double p = fma(r, 1.0 / 24.0, 1.0 / 6.0);
   p = fma(p, r, 0.5);
   p = fma(p, r, 1.0);
@@ -535,30 +537,43 @@ __device__ __forceinline__ double rcp_cubic(double x) {
   return fma(r, e, r);
 }
 
+// -N lc_j V_j for one line in the far wing, NT-term series (NT = 3: |x| >= 256; 4: >= 64):
+//   ncw sp (1 + g1p sp + g2 sp^2 [+ g3 sp^3]),  g1p = g1 - y2T_j
 template <int NT>
-__device__ __forceinline__ double wing_term_n(double sp, int j, double ncw, double total) {
+__device__ __forceinline__ double wing_far(double sp, int j, double ncw, double total) {
   double G = g_lines.gq[NT - 1];
 #pragma unroll
-  for (int n = NT - 2; n >= 0; --n) G = fma(G, sp, g_lines.gq[n]);
-  if (NT == 7) G -= (g_lines.y2T[j] * sp) * fma(g_lines.fiveT, sp, 1.0);
-  else G = fma(-g_lines.y2T[j], sp, G);
+  for (int n = NT - 2; n >= 2; --n) G = fma(G, sp, g_lines.gq[n]);
+  G = fma(G, sp, g_lines.g1p[j]);
+  G = fma(G, sp, 1.0);
+  return fma(ncw, G * sp, total);
+}
+__device__ __forceinline__ double wing_7(double sp, int j, double ncw, double total) {
+  double G = g_lines.gq[6];
+#pragma unroll
+  for (int n = 5; n >= 0; --n) G = fma(G, sp, g_lines.gq[n]);
+  G -= (g_lines.y2T[j] * sp) * fma(g_lines.fiveT, sp, 1.0);
   return fma(ncw * sp, G, total);
 }
 
 // raw transmission exp(-N sum_j tau_j) of NPIX wavelengths for this lane's hypothesis
 // (voigt.c:282-292).  ncw[j] = -N cwT_j.  Must be called by all 32 lanes.
+// The velocity is formed with ONE fma first; beyond 64 Doppler widths that differs from voigt.c:287's
+// separately rounded product by <= 2^-53 c / v <= 4e-14 relative.  Closer to a line the step is
+// redone with the reference's rounding (warp-uniform branch, rare).
 template <int NPIX>
 __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const double (&mult)[3],
                                          const double (&ncw)[3], double N, const double* etab_s,
                                          double (&out)[NPIX]) {
   double sp[NPIX][3];
   int minhi = 0x7fffffff;
+  const double negc = -g_lines.c_cgs;
 #pragma unroll
   for (int p = 0; p < NPIX; ++p) {
     double v2[3];
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
-      const double velocity = __dsub_rn(__dmul_rn(lambda[p], mult[j]), g_lines.c_cgs);  // voigt.c:287
+      const double velocity = fma(lambda[p], mult[j], negc);
       v2[j] = velocity * velocity;
       minhi = min(minhi, __double2hiint(v2[j]));
     }
@@ -577,18 +592,27 @@ __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const dou
 #pragma unroll
     for (int j = 0; j < 3; ++j)
 #pragma unroll
-      for (int p = 0; p < NPIX; ++p) total[p] = wing_term_n<3>(sp[p][j], j, ncw[j], total[p]);
-  } else if (wmin >= g_lines.hi_64) {
+      for (int p = 0; p < NPIX; ++p) total[p] = wing_far<3>(sp[p][j], j, ncw[j], total[p]);
+  } else if (wmin >= g_lines.hi_64x) {
 #pragma unroll
     for (int j = 0; j < 3; ++j)
 #pragma unroll
-      for (int p = 0; p < NPIX; ++p) total[p] = wing_term_n<4>(sp[p][j], j, ncw[j], total[p]);
+      for (int p = 0; p < NPIX; ++p) total[p] = wing_far<4>(sp[p][j], j, ncw[j], total[p]);
   } else {
+    // within ~64 widths of a line for some lane: the reference's velocity rounding, 7-term series,
+    // and the exact two-regime path for the lanes with a line core (|x| < 16) in these pixels
+    bool near = false;
 #pragma unroll
-    for (int j = 0; j < 3; ++j)
+    for (int p = 0; p < NPIX; ++p) {
 #pragma unroll
-      for (int p = 0; p < NPIX; ++p) total[p] = wing_term_n<7>(sp[p][j], j, ncw[j], total[p]);
-    if (minhi < g_lines.hi_near) {  // a line core within this lane's pixels: exact two-regime path
+      for (int j = 0; j < 3; ++j) {
+        const double velocity = __dsub_rn(__dmul_rn(lambda[p], mult[j]), g_lines.c_cgs);  // voigt.c:287
+        const double v2e = velocity * velocity;
+        near = near || (__double2hiint(v2e) < g_lines.hi_near);
+        total[p] = wing_7(rcp_cubic(v2e), j, ncw[j], total[p]);
+      }
+    }
+    if (near) {
 #pragma unroll
       for (int p = 0; p < NPIX; ++p) {
         double t = 0.0;
