@@ -82,7 +82,6 @@ struct dla_ctx {
   bool force_pixel_lane_k1 = false;  // DLA_B200_K1=pixel: always use voigt_weights_kernel
   bool force_tile_k2 = false;        // DLA_B200_K2=tile: one CTA per tile (contract_chol_kernel)
   int num_sms = 148;
-  int k1_sb_per_cta = 1;
   // staged batch
   int64_t Q = 0;
   bool staged = false, ran = false;
@@ -164,15 +163,15 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     dla::pack_pixels_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[1], st));
+  int nseg = 1;  // partial (q0, log|D|) sums per sample that K1 leaves in aux
   if (ch.all_ident && num_lines == 3 && !c->force_pixel_lane_k1) {
-    const int sb_per_cta = c->k1_sb_per_cta;
-    const int nsbg = (nsb + sb_per_cta - 1) / sb_per_cta;
-    const int lam_cap = (int)round_up(ch.max_P, 2);
-    const size_t smem = ((size_t)lam_cap + 4 * (size_t)ch.max_npad) * 8;
+    nseg = std::min(dla::K1S_NSEG_MAX, std::max(dla::K1S_NSEG_MIN, (ch.max_npad / 4 + 79) / 80));
+    const int gmax = (ch.max_npad / 4 + nseg - 1) / nseg + 1;  // groups of 4 pixels per segment
+    const int lam_cap = 4 * gmax + 8;
+    const size_t smem = ((size_t)lam_cap + 16 * (size_t)gmax) * 8;
     if (smem > 100 * 1024) BAD_ARG(c, "a quasar has too many pixels for the Voigt kernel's shared-memory staging");
-    dla::voigt_weights_lane_kernel<<<(unsigned)((int64_t)ch.nq * nsbg), dla::K1S_THREADS, smem, st>>>(
-        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_etab256.as<double>(), W, U, aux,
-        sb_per_cta, lam_cap);
+    dla::voigt_weights_lane_kernel<<<(unsigned)((int64_t)ch.nq * nsb * nseg), dla::K1S_THREADS, smem, st>>>(
+        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_etab256.as<double>(), W, U, aux, lam_cap, nseg);
   } else {
     const int raw_stride = (int)round_up(ch.max_P, 2) + 2;  // +2: the 16-byte window loads of the tail may touch one double past P
     const int warps = k1_warps_for(raw_stride);
@@ -191,16 +190,16 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     dim3 g2((unsigned)((S + 1 + dla::CHG_WARPS - 1) / dla::CHG_WARPS), (unsigned)ch.nq);
     const size_t sm2 = (size_t)dla::CHG_WARPS * (k + 1) * (k + 2) * 8;
     dla::chol_generic_kernel<<<g2, dla::CHG_WARPS * 32, sm2, st>>>(in.desc, ch.q0, nsb, S, c->d_G.as<double>(), aux,
-                                                                    d_perm, sample_ll_chunk, ll_no, k, gen.ncol, gen.voff);
+                                                                    d_perm, sample_ll_chunk, ll_no, k, gen.ncol, gen.voff, nseg);
   } else if (!c->force_tile_k2) {
     const int64_t ntiles = (int64_t)ch.nq * nsb;
     const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
     dla::contract_chol_persistent_kernel<<<grid, dla::K2P_THREADS, dla::K2P_SMEM_BYTES, st>>>(
-        in.desc, ch.q0, nsb, (int)ntiles, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k);
+        in.desc, ch.q0, nsb, (int)ntiles, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k, nseg);
   } else {
     const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
     dla::contract_chol_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K2_THREADS, smem, st>>>(
-        in.desc, ch.q0, nsb, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k);
+        in.desc, ch.q0, nsb, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k, nseg);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[3], st));
   if (S > 0 && ll_dla) {
@@ -247,7 +246,7 @@ static int ensure_workspace(dla_ctx* c, int k, int64_t wu_doubles, int64_t bmat_
   CU_TRY(c, c->d_U.ensure((size_t)wu_doubles * 8));
   const ColGeom gen = col_geom(k);
   CU_TRY(c, c->d_bmat.ensure((size_t)(bmat_doubles / dla::NCOL + 1) * gen.ncol * 8));
-  CU_TRY(c, c->d_aux.ensure((size_t)nq * 2 * S_pad * 8));
+  CU_TRY(c, c->d_aux.ensure((size_t)nq * 2 * dla::K1S_NSEG_MAX * S_pad * 8));
   if (gen.generic) CU_TRY(c, c->d_G.ensure((size_t)nq * S_pad * gen.ncol * 8));
   if (need_ll_chunk) CU_TRY(c, c->d_ll_chunk.ensure((size_t)std::max<int64_t>(1, (int64_t)nq * S) * 8));
   return DLA_OK;
@@ -389,7 +388,6 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     const char* k2 = getenv("DLA_B200_K2");
     c->force_tile_k2 = k2 && strcmp(k2, "tile") == 0;
     c->num_sms = prop.multiProcessorCount;
-    if (const char* e = getenv("DLA_B200_K1_SB")) c->k1_sb_per_cta = std::max(1, atoi(e));
     const char* k1 = getenv("DLA_B200_K1");
     c->force_pixel_lane_k1 = k1 && strcmp(k1, "pixel") == 0;
   }

@@ -502,13 +502,14 @@ voigt_weights_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
 //   * W/U leave as 32-byte per-lane records that are contiguous across the warp in the
 //     DMMA-fragment layout [pixel/4][64 samples][4 pixels],
 //   * q0 and log|D| are private running sums (one cross-segment reduction per CTA at the end).
-// CTA = 64 hypotheses (one sample block) x K1S_NSEG spectrum segments.  Requires the as-written
+// CTA = 64 hypotheses (one sample block) x ONE of K1S_NSEG spectrum segments (segments near a line
+// core take longer; independent CTAs let the block scheduler balance that).  Requires the as-written
 // gather (profile_index[j] == j) and num_lines == 3; anything else takes voigt_weights_kernel.
 // Hypotheses s >= S of the last block (the no-DLA pseudo-sample s == S and the padding rows) run
 // with N = 0, which gives a == 1 exactly (process_qsos.m:150-152).
 // ----------------------------------------------------------------------------------------------
-constexpr int K1S_NSEG = 4;
-constexpr int K1S_THREADS = TS * K1S_NSEG;
+constexpr int K1S_NSEG_MIN = 4, K1S_NSEG_MAX = 16;  // spectrum segments per sample block (~<= 80 pixel groups each)
+constexpr int K1S_THREADS = TS;  // one CTA = 64 hypotheses x ONE spectrum segment
 
 // exp(t), t <= 0, result >= 2^-1020 (t is clamped at -707: a transmission of 1e-307 and one of 0
 // are the same number to every consumer: a^2 underflows either way).  NaN propagates.
@@ -628,7 +629,7 @@ __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const dou
 
 // weights of the four kept pixels 4g..4g+3 from the 10-point window raw[4g .. 4g+9]
 template <bool TAIL>
-__device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int n, const double2* px /* shared */,
+__device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int n, int jdead, const double2* px /* shared */,
                                              double* __restrict__ wp, double* __restrict__ up, double& q0acc,
                                              double& ldacc, double& dprod, int& esum) {
   double w[4], u[4], dd[4];
@@ -637,7 +638,7 @@ __device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int
   for (int h = 0; h < 4; ++h) {
     const int j = 4 * g + h;
     const bool live = !TAIL || j < n;
-    const int jc = live ? j : 0;
+    const int jc = live ? j : jdead;
     const double2 p01 = px[2 * jc];      // {omega2, noise}
     const double2 p23 = px[2 * jc + 1];  // {mu, flux}
     double a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
@@ -684,33 +685,36 @@ __device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int
   reinterpret_cast<double2*>(up)[1] = make_double2(u[2], u[3]);
 }
 
-__global__ void __launch_bounds__(K1S_THREADS, 2)
+__global__ void __launch_bounds__(K1S_THREADS, 8)
 voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
                           const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
                           const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
                           const double* __restrict__ etab256, double* __restrict__ Wbuf,
-                          double* __restrict__ Ubuf, double* __restrict__ aux, int sb_per_cta, int lam_cap) {
-  // shared: the quasar's padded wavelengths [lam_cap] and packed pixel records [n][4] (every lane of
-  // the CTA reads the same addresses: broadcast LDS instead of global loads), then the exp table
+                          double* __restrict__ Ubuf, double* __restrict__ aux, int lam_cap, int nseg) {
+  // shared: this segment's slice of the padded wavelengths [lam_cap] and of the packed pixel records
+  // (every lane reads the same addresses: broadcast LDS instead of global loads), and the exp table
   extern __shared__ __align__(16) double k1s_smem[];
   __shared__ double etab_s[256];
-  __shared__ double red_s[K1S_NSEG][TS][2];
-  const int nsbg = (nsb + sb_per_cta - 1) / sb_per_cta;
-  const int ql = blockIdx.x / nsbg, sbg = blockIdx.x % nsbg;
+  const int seg = blockIdx.x % nseg;
+  const int tile = blockIdx.x / nseg;
+  const int ql = tile / nsb, sb = tile % nsb;
   const QuasarDesc d = desc[q0 + ql];
   const int tid = threadIdx.x;
+  const int npc = d.npad >> 2, n = d.n, Pm1 = d.P - 1;
+  const int g0 = (int)(((int64_t)seg * npc) / nseg), g1 = (int)(((int64_t)(seg + 1) * npc) / nseg);
+  const int lbase = max(4 * g0 - 2, 0), llast = min(4 * g1 + 5, Pm1);  // wavelengths this segment touches
+  const int j0 = 4 * g0, j1 = min(4 * g1, n);                          // kept pixels this segment emits
   double* lam_s = k1s_smem;
   double2* px_s = reinterpret_cast<double2*>(k1s_smem + lam_cap);
-  etab_s[tid & 255] = etab256[tid & 255];
+  for (int i = tid; i < 256; i += K1S_THREADS) etab_s[i] = etab256[i];
   {
-    const double* lam_g = padded_wavelengths + d.pad_off;
-    for (int i = tid; i < d.P; i += K1S_THREADS) lam_s[i] = __ldg(lam_g + i);
-    const double2* px_g = pix4 + 2 * d.pix_off;
-    for (int i = tid; i < 2 * d.n; i += K1S_THREADS) px_s[i] = __ldg(px_g + i);
+    const double* lam_g = padded_wavelengths + d.pad_off + lbase;
+    for (int i = tid; i <= llast - lbase; i += K1S_THREADS) lam_s[i] = __ldg(lam_g + i);
+    const double2* px_g = pix4 + 2 * (d.pix_off + j0);
+    for (int i = tid; i < 2 * (j1 - j0); i += K1S_THREADS) px_s[i] = __ldg(px_g + i);
   }
   __syncthreads();
-  const int srow = tid & (TS - 1), seg = tid / TS;
-  for (int sb = sbg * sb_per_cta; sb < min(nsb, (sbg + 1) * sb_per_cta); ++sb) {
+  const int srow = tid;
   const int64_t s = (int64_t)sb * TS + srow;
   const bool real = s < S;
   // process_qsos.m:163-165: min + (max - min) * offset, separately rounded
@@ -724,10 +728,8 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
     mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;  // voigt.c:278-279
     ncw[j] = -N * g_lines.cwT[j];
   }
-  const double* lam = lam_s;
-  const double2* px = px_s;
-  const int npc = d.npad >> 2, n = d.n, Pm1 = d.P - 1;
-  const int g0 = (int)(((int64_t)seg * npc) / K1S_NSEG), g1 = (int)(((int64_t)(seg + 1) * npc) / K1S_NSEG);
+  const double* lam = lam_s - lbase;            // indexed by the padded-grid position
+  const double2* px = px_s - 2 * j0;            // indexed by 2 * kept pixel
   const int gfull = n >> 2;  // groups [0, gfull) have four live pixels
   const int64_t S_pad = (int64_t)nsb * TS;
   double* wp = Wbuf + d.wu_off + ((int64_t)sb * npc + g0) * (TS * 4) + srow * 4;
@@ -745,7 +747,7 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
     const int b = 4 * (g0 + st) - 2;
     double l4[4], r4[4];
 #pragma unroll
-    for (int h = 0; h < 4; ++h) l4[h] = lam[min(max(b + h, 0), Pm1)];
+    for (int h = 0; h < 4; ++h) l4[h] = lam[min(max(b + h, lbase), llast)];
     raw_lane<4>(l4, mult, ncw, N, etab_s, r4);
 #pragma unroll
     for (int t = 0; t < 6; ++t) win[t] = win[t + 4];
@@ -753,26 +755,17 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
     for (int h = 0; h < 4; ++h) win[6 + h] = r4[h];
     if (st >= 2) {
       const int g = g0 + st - 2;
-      if (g < gfull) weights_lane<false>(win, g, n, px, wp, up, q0acc, ldacc, dprod, esum);
-      else weights_lane<true>(win, g, n, px, wp, up, q0acc, ldacc, dprod, esum);
+      if (g < gfull) weights_lane<false>(win, g, n, j0, px, wp, up, q0acc, ldacc, dprod, esum);
+      else weights_lane<true>(win, g, n, j0, px, wp, up, q0acc, ldacc, dprod, esum);
       wp += TS * 4;
       up += TS * 4;
     }
   }
   ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
-  red_s[seg][srow][0] = q0acc;
-  red_s[seg][srow][1] = ldacc;
-  __syncthreads();
-  if (tid < TS) {
-    double a0 = 0.0, a1 = 0.0;
-#pragma unroll
-    for (int g = 0; g < K1S_NSEG; ++g) { a0 += red_s[g][tid][0]; a1 += red_s[g][tid][1]; }
-    double* auxq = aux + (int64_t)ql * 2 * S_pad;
-    auxq[s] = a0;
-    auxq[S_pad + s] = a1;
-  }
-  __syncthreads();  // red_s is reused by the next sample block
-  }
+  // per-segment partial sums; K2 adds the nseg partials in a fixed order
+  double* auxq = aux + (int64_t)ql * 2 * nseg * S_pad;
+  auxq[(int64_t)seg * S_pad + s] = q0acc;
+  auxq[(int64_t)(nseg + seg) * S_pad + s] = ldacc;
 }
 
 // Single-profile seam (dla_voigt = the voigt MEX, voigt.c:253-304). One CTA.
@@ -827,6 +820,19 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
   asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
       : "+d"(c0), "+d"(c1)
       : "d"(a), "d"(b));
+}
+
+// q0 / log|D| of sorted sample s: K1 leaves nseg partial sums each ([2 nseg][S_pad] per quasar), added here
+// in a fixed order
+__device__ __forceinline__ void aux_sums(const double* __restrict__ aux, int ql, int nseg, int64_t S_pad, int64_t s,
+                                         double& q0v, double& ldv) {
+  const double* auxq = aux + (int64_t)ql * 2 * nseg * S_pad + s;
+  q0v = 0.0;
+  ldv = 0.0;
+  for (int g = 0; g < nseg; ++g) {
+    q0v += auxq[(int64_t)g * S_pad];
+    ldv += auxq[(int64_t)(nseg + g) * S_pad];
+  }
 }
 
 // Packed lower-triangular index, row i >= column l.
@@ -899,7 +905,7 @@ contract_chol_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
                      const double* __restrict__ bmat, const double* __restrict__ aux,
                      const int32_t* __restrict__ perm /* sorted position -> caller's sample index */,
                      double* __restrict__ sample_ll /* [Qc][S] chunk-local */,
-                     double* __restrict__ ll_no_dla /* [Q] batch-global */, int k) {
+                     double* __restrict__ ll_no_dla /* [Q] batch-global */, int k, int nseg) {
   extern __shared__ __align__(128) unsigned char k2_smem_raw[];
   double* smem = reinterpret_cast<double*>(k2_smem_raw);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)K2_STAGES * STAGE_DOUBLES);
@@ -993,8 +999,8 @@ contract_chol_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
     const int srow = tid >> 2, t = tid & 3;
     const int64_t s = (int64_t)sb * TS + srow;
     const int64_t S_pad = (int64_t)nsb * TS;
-    const double* auxq = aux + (int64_t)ql * 2 * S_pad;
-    const double q0v = auxq[s], ldv = auxq[S_pad + s];
+    double q0v, ldv;
+    aux_sums(aux, ql, nseg, S_pad, s, q0v, ldv);
     const double lp = chol_logp_quad(Cs + (size_t)srow * LDC, k, t, q0v, ldv, d.n);
     if (t == 0) {
       if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
@@ -1034,7 +1040,7 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
                                 const double* __restrict__ Wbuf, const double* __restrict__ Ubuf,
                                 const double* __restrict__ bmat, const double* __restrict__ aux,
                                 const int32_t* __restrict__ perm, double* __restrict__ sample_ll,
-                                double* __restrict__ ll_no_dla, int k) {
+                                double* __restrict__ ll_no_dla, int k, int nseg) {
   extern __shared__ __align__(128) unsigned char k2_smem_raw[];
   double* smem = reinterpret_cast<double*>(k2_smem_raw);
   double* Cs = smem + (size_t)K2P_STAGES * K2P_STAGE_DOUBLES;
@@ -1145,8 +1151,8 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
       const int srow = tid >> 2, q4 = tid & 3;
       const int64_t s = (int64_t)sb * TS + srow;
       const int64_t S_pad = (int64_t)nsb * TS;
-      const double* auxq = aux + (int64_t)ql * 2 * S_pad;
-      const double q0v = auxq[s], ldv = auxq[S_pad + s];
+      double q0v, ldv;
+      aux_sums(aux, ql, nseg, S_pad, s, q0v, ldv);
       const double lp = chol_logp_quad<true>(Cs + (size_t)srow * LDC, k, q4, q0v, ldv, n);
       if (q4 == 0) {
         if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
@@ -1264,7 +1270,7 @@ constexpr int CHG_WARPS = 4;
 __global__ void __launch_bounds__(CHG_WARPS * 32)
 chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S, const double* __restrict__ Gbuf,
                     const double* __restrict__ aux, const int32_t* __restrict__ perm, double* __restrict__ sample_ll,
-                    double* __restrict__ ll_no_dla, int k, int ncol, int voff) {
+                    double* __restrict__ ll_no_dla, int k, int ncol, int voff, int nseg) {
   extern __shared__ double chg_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ld = k + 2, kb = k + 1;
@@ -1274,11 +1280,12 @@ chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_
   const int64_t s = (int64_t)blockIdx.x * CHG_WARPS + warp;
   if (s > S) return;  // whole warp
   const double* row = Gbuf + ((int64_t)ql * S_pad + s) * ncol;
-  const double* auxq = aux + (int64_t)ql * 2 * S_pad;
+  double q0v, ldv;
+  aux_sums(aux, ql, nseg, S_pad, s, q0v, ldv);
   for (int i = 0; i < k; ++i)
     for (int l = lane; l <= i; l += 32) A[i * ld + l] = row[((i * (i + 1)) >> 1) + l] + (l == i ? 1.0 : 0.0);
   for (int l = lane; l < k; l += 32) A[k * ld + l] = row[voff + l];
-  if (lane == 0) A[k * ld + k] = auxq[s];
+  if (lane == 0) A[k * ld + k] = q0v;
   __syncwarp();
   double pprod = 1.0;
   int esum = 0;
@@ -1305,7 +1312,7 @@ chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_
   if (lane == 0) {
     const double qq = A[k * ld + k];
     const double logdet = fma((double)esum, 0.693147180559945309417232, log(pprod));
-    const double lp = -0.5 * (qq + (auxq[S_pad + s] + logdet) + (double)desc[q0 + ql].n * LOG_2PI);
+    const double lp = -0.5 * (qq + (ldv + logdet) + (double)desc[q0 + ql].n * LOG_2PI);
     if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
     else ll_no_dla[q0 + ql] = lp;
   }
