@@ -18,7 +18,7 @@ STATUS_NAMES = {0: "DLA_OK", -1: "DLA_ERR_BAD_ARG", -2: "DLA_ERR_CUDA", -3: "DLA
 EXPORTED_SYMBOLS = (
     "dla_abi_version", "dla_device_count", "dla_create", "dla_destroy", "dla_last_error",
     "dla_set_samples", "dla_eval_batch", "dla_stage_batch", "dla_run_staged", "dla_fetch_staged",
-    "dla_get_timing", "dla_voigt", "dla_log_mvnpdf_low_rank",
+    "dla_get_timing", "dla_voigt", "dla_log_mvnpdf_low_rank", "dla_set_model", "dla_eval_spectra",
 )
 
 
@@ -31,6 +31,13 @@ class DlaError(RuntimeError):
 class dla_params(C.Structure):
     _fields_ = [("k", C.c_int32), ("num_lines", C.c_int32), ("num_samples", C.c_int64),
                 ("store_sample_ll", C.c_int32), ("reserved", C.c_int32), ("workspace_bytes", C.c_int64)]
+
+
+class dla_prep_params(C.Structure):
+    _fields_ = [("min_lambda", C.c_double), ("max_lambda", C.c_double), ("lya_wavelength", C.c_double),
+                ("lyman_limit", C.c_double), ("max_z_cut", C.c_double), ("min_z_cut", C.c_double),
+                ("pixel_spacing", C.c_double), ("width", C.c_int32), ("reserved", C.c_int32),
+                ("log_c_0", C.c_double), ("log_tau_0", C.c_double), ("log_beta", C.c_double)]
 
 
 class dla_timing(C.Structure):
@@ -90,6 +97,11 @@ def load() -> C.CDLL:
     lib.dla_voigt.argtypes = [_ctx, _pd, C.c_int64, C.c_double, C.c_double, C.c_int32, _pd]
     lib.dla_log_mvnpdf_low_rank.restype = C.c_int
     lib.dla_log_mvnpdf_low_rank.argtypes = [_ctx, _pd, _pd, _pd, _pd, C.c_int64, C.c_int32, _pd]
+    lib.dla_set_model.restype = C.c_int
+    lib.dla_set_model.argtypes = [_ctx, C.c_int64, _pd, _pd, _pd, _pd, C.POINTER(dla_prep_params)]
+    lib.dla_eval_spectra.restype = C.c_int
+    lib.dla_eval_spectra.argtypes = ([_ctx, C.c_int64, _pi64, _pd, _pd, _pd, C.POINTER(C.c_uint8), _pd, _pd, _pd, C.c_int32]
+                                     + _OUTPUTS + [_pd, _pd])
     _lib = lib
     return lib
 

@@ -73,7 +73,13 @@ struct dla_ctx {
     const int64_t *pix_ptr, *pad_ptr;
     const double *padded, *flux, *mu, *om, *nv, *M;
     const int32_t* pidx;
+    const double *lamk, *zq;  // device-prep mode: kept wavelengths [sum n_q], z_qso [Q]
   } hin{};
+  // learned model for the device-side preparation (dla_set_model)
+  bool have_model = false, dev_prep = false;
+  int64_t n_rest = 0;
+  dla_prep_params prep{};
+  DevBuf d_mrest, d_mmu, d_mM, d_mlo, d_lamk, d_zq;
   // hypothesis set
   // (sorted by offset once: the hypotheses of a warp are then neighbours in z; d_perm maps a
   //  sorted position back to the caller's sample index)
@@ -412,7 +418,8 @@ void dla_destroy(dla_ctx* c) {
   cudaStreamSynchronize(c->stream);
   for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_perm, &c->d_etab256, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
                     &c->d_nv, &c->d_M, &c->d_pix4, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
-                    &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk, &c->d_G})
+                    &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk, &c->d_G,
+                    &c->d_mrest, &c->d_mmu, &c->d_mM, &c->d_mlo, &c->d_lamk, &c->d_zq})
     b->release();
   for (auto& ev : c->ev)
     if (ev) cudaEventDestroy(ev);
@@ -566,7 +573,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
   }
   int rc = ensure_events(c, std::max<size_t>(1, c->chunks.size()));
   if (rc != DLA_OK) return rc;
-  c->hin = {pix_ptr, pad_ptr, padded_wavelengths, flux, mu, omega2, noise_variance, M, profile_index};
+  c->hin = {pix_ptr, pad_ptr, padded_wavelengths, flux, mu, omega2, noise_variance, M, profile_index, nullptr, nullptr};
   c->Q = Q;
   c->timing = dla_timing{};
   return DLA_OK;
@@ -589,10 +596,15 @@ static int upload_chunk(dla_ctx* c, size_t i, cudaStream_t st) {
   CU_TRY(c, up(c->d_padded, h.padded, (size_t)w0 * 8, (size_t)(w1 - w0) * 8));
   CU_TRY(c, up(c->d_pidx, h.pidx, (size_t)p0 * 4, (size_t)(p1 - p0) * 4));
   CU_TRY(c, up(c->d_flux, h.flux, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
-  CU_TRY(c, up(c->d_mu, h.mu, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
-  CU_TRY(c, up(c->d_om, h.om, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
   CU_TRY(c, up(c->d_nv, h.nv, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
-  CU_TRY(c, up(c->d_M, h.M, (size_t)p0 * k * 8, (size_t)(p1 - p0) * k * 8));
+  if (c->dev_prep) {  // mu, omega2, M are interpolated on the device from the resident model
+    if (i == 0) CU_TRY(c, up(c->d_zq, h.zq, 0, (size_t)c->Q * 8));
+    CU_TRY(c, up(c->d_lamk, h.lamk, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
+  } else {
+    CU_TRY(c, up(c->d_mu, h.mu, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
+    CU_TRY(c, up(c->d_om, h.om, (size_t)p0 * 8, (size_t)(p1 - p0) * 8));
+    CU_TRY(c, up(c->d_M, h.M, (size_t)p0 * k * 8, (size_t)(p1 - p0) * k * 8));
+  }
   CU_TRY(c, cudaEventRecord(c->ev_sync[2 * i], st));
   return DLA_OK;
 }
@@ -605,6 +617,16 @@ static int run_chunk(dla_ctx* c, size_t i) {
             c->d_om.as<double>(), c->d_nv.as<double>(), c->d_M.as<double>(), c->d_pidx.as<int32_t>(),
             c->d_pix4.as<double2>()};
   CU_TRY(c, cudaStreamWaitEvent(c->stream, c->ev_sync[2 * i], 0));
+  if (c->dev_prep) {
+    const dla_prep_params& pp = c->prep;
+    dla::PrepConsts pc{pp.lya_wavelength, exp(pp.log_c_0), exp(pp.log_tau_0), exp(pp.log_beta)};  // process_qsos.m:84-86
+    dim3 grid((unsigned)((ch.max_npad + 127) / 128), (unsigned)ch.nq);
+    dla::prep_model_kernel<<<grid, 128, 0, c->stream>>>(
+        in.desc, ch.q0, c->d_zq.as<double>(), c->d_lamk.as<double>(), (int)c->n_rest, c->d_mrest.as<double>(),
+        c->d_mmu.as<double>(), c->d_mM.as<double>(), c->d_mlo.as<double>(), pc, c->p.k, c->d_mu.as<double>(),
+        c->d_om.as<double>(), c->d_M.as<double>());
+    c->timing.launches += 1;
+  }
   double* ll_chunk = c->p.store_sample_ll ? c->d_sample_ll.as<double>() + (int64_t)ch.q0 * S : c->d_ll_chunk.as<double>();
   int rc = launch_chunk(c, in, ch, S, c->p.k, c->p.num_lines, c->d_offset.as<double>(), c->d_nhi.as<double>(),
                         c->d_perm.as<int32_t>(), ll_chunk, c->d_ll_no.as<double>(), c->d_ll_dla.as<double>(),
@@ -622,6 +644,7 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
                     const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
                     const double* log_prior_no_dla) {
   if (!c) return DLA_ERR_BAD_ARG;
+  c->dev_prep = false;
   int rc = plan_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M,
                       min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
   if (rc != DLA_OK) return rc;
@@ -707,17 +730,9 @@ int dla_fetch_staged(dla_ctx* c, double* sample_ll, double* ll_no_dla, double* l
 
 // One call, pipelined over the chunks: H2D of chunk i+1 (stream s_in) and D2H of chunk i-1's
 // sample log-likelihoods (stream s_out) run under the kernels of chunk i (compute stream).
-int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
-                   const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
-                   const double* mu, const double* omega2, const double* noise_variance, const double* M,
-                   const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
-                   const double* log_prior_no_dla, double* sample_ll, double* ll_no_dla, double* ll_dla,
-                   double* log_post_no_dla, double* log_post_dla, double* model_posteriors, int32_t* map_index) {
-  if (!c) return DLA_ERR_BAD_ARG;
-  if (sample_ll && !c->p.store_sample_ll) BAD_ARG(c, "dla_eval_batch: sample_ll requested but store_sample_ll = 0");
-  int rc = plan_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M,
-                      min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
-  if (rc != DLA_OK) return rc;
+static int run_pipelined(dla_ctx* c, double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
+                         double* log_post_dla, double* model_posteriors, int32_t* map_index) {
+  int rc = DLA_OK;
   const int64_t S = c->p.num_samples;
   const size_t nch = c->chunks.size();
   CU_TRY(c, cudaEventRecord(c->ev[5], c->s_in));
@@ -748,6 +763,136 @@ int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t*
   if ((rc = collect_timing(c, nch)) != DLA_OK) return rc;
   c->staged = true;
   c->ran = true;
+  return DLA_OK;
+}
+
+int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
+                   const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
+                   const double* mu, const double* omega2, const double* noise_variance, const double* M,
+                   const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
+                   const double* log_prior_no_dla, double* sample_ll, double* ll_no_dla, double* ll_dla,
+                   double* log_post_no_dla, double* log_post_dla, double* model_posteriors, int32_t* map_index) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (sample_ll && !c->p.store_sample_ll) BAD_ARG(c, "dla_eval_batch: sample_ll requested but store_sample_ll = 0");
+  c->dev_prep = false;
+  int rc = plan_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M,
+                      min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
+  if (rc != DLA_OK) return rc;
+  return run_pipelined(c, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
+}
+
+int dla_set_model(dla_ctx* c, int64_t n_rest, const double* rest_wavelengths, const double* mu, const double* M,
+                  const double* log_omega, const dla_prep_params* prep) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!rest_wavelengths || !mu || !M || !log_omega || !prep) BAD_ARG(c, "dla_set_model: NULL pointer");
+  if (n_rest < 2 || n_rest > (1 << 24)) BAD_ARG(c, "dla_set_model: n_rest out of range");
+  if (prep->width != 3) BAD_ARG(c, "dla_set_model: width must be 3 (the instrument profile of voigt.c:229 has 7 taps)");
+  for (int64_t i = 1; i < n_rest; ++i)
+    if (!(rest_wavelengths[i] > rest_wavelengths[i - 1])) BAD_ARG(c, "dla_set_model: rest_wavelengths must be strictly increasing");
+  CU_TRY(c, cudaSetDevice(c->device));
+  const int k = c->p.k;
+  CU_TRY(c, c->d_mrest.ensure((size_t)n_rest * 8));
+  CU_TRY(c, c->d_mmu.ensure((size_t)n_rest * 8));
+  CU_TRY(c, c->d_mlo.ensure((size_t)n_rest * 8));
+  CU_TRY(c, c->d_mM.ensure((size_t)n_rest * k * 8));
+  CU_TRY(c, cudaMemcpyAsync(c->d_mrest.p, rest_wavelengths, (size_t)n_rest * 8, cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemcpyAsync(c->d_mmu.p, mu, (size_t)n_rest * 8, cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemcpyAsync(c->d_mlo.p, log_omega, (size_t)n_rest * 8, cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemcpyAsync(c->d_mM.p, M, (size_t)n_rest * k * 8, cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  c->n_rest = n_rest;
+  c->prep = *prep;
+  c->have_model = true;
+  return DLA_OK;
+}
+
+int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const double* wavelengths, const double* flux,
+                     const double* noise_variance, const uint8_t* pixel_mask, const double* z_qso,
+                     const double* log_prior_dla, const double* log_prior_no_dla, int32_t mask_gather,
+                     double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
+                     double* log_post_dla, double* model_posteriors, int32_t* map_index, double* min_z_out,
+                     double* max_z_out) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!c->have_model) {
+    c->err = "dla_eval_spectra: dla_set_model has not been called";
+    return DLA_ERR_STATE;
+  }
+  if (Q < 0 || !spec_ptr || !wavelengths || !flux || !noise_variance || !pixel_mask || !z_qso || !log_prior_dla ||
+      !log_prior_no_dla)
+    BAD_ARG(c, "dla_eval_spectra: NULL pointer");
+  if (mask_gather != 0 && mask_gather != 1) BAD_ARG(c, "dla_eval_spectra: mask_gather must be 0 or 1");
+  if (sample_ll && !c->p.store_sample_ll) BAD_ARG(c, "dla_eval_spectra: sample_ll requested but store_sample_ll = 0");
+  const dla_prep_params& pp = c->prep;
+  // one host pass per quasar: process_qsos.m:102-116 (selection), :160-161 (z range), :169-180 (padded grid, gather)
+  std::vector<int64_t> pix_ptr((size_t)Q + 1, 0), pad_ptr((size_t)Q + 1, 0);
+  std::vector<double> lamk, fk, nk, padded, minz((size_t)Q), maxz((size_t)Q);
+  std::vector<int32_t> pidx;
+  const int64_t ntot = spec_ptr[Q] - spec_ptr[0];
+  lamk.reserve((size_t)ntot); fk.reserve((size_t)ntot); nk.reserve((size_t)ntot); pidx.reserve((size_t)ntot);
+  padded.reserve((size_t)ntot + 6 * (size_t)Q);
+  for (int64_t q = 0; q < Q; ++q) {
+    const int64_t a = spec_ptr[q], b = spec_ptr[q + 1];
+    if (b < a) BAD_ARG(c, "dla_eval_spectra: spec_ptr must be non-decreasing");
+    const double opz = 1.0 + z_qso[q];
+    const size_t pad0 = padded.size();
+    padded.resize(pad0 + 3);  // left pads, filled below
+    int64_t n_full = 0, n = 0;
+    double umin = INFINITY, umax = -INFINITY, kmin = INFINITY, kmax = -INFINITY;
+    for (int64_t i = a; i < b; ++i) {
+      const double rest = wavelengths[i] / opz;                              // :102, set_parameters.m:14-15
+      if (!(rest >= pp.min_lambda && rest <= pp.max_lambda)) continue;        // :104-105
+      const double w = wavelengths[i];
+      padded.push_back(w);                                                    // :109 this_unmasked_wavelengths
+      umin = std::min(umin, w); umax = std::max(umax, w);
+      if (!pixel_mask[i]) {                                                   // :111-116
+        lamk.push_back(w); fk.push_back(flux[i]); nk.push_back(noise_variance[i]);
+        pidx.push_back((int32_t)(mask_gather ? n_full : n));                  // :180/:189 as written, or the unmasked positions
+        kmin = std::min(kmin, w); kmax = std::max(kmax, w);
+        ++n;
+      }
+      ++n_full;
+    }
+    if (n_full == 0 || n == 0) BAD_ARG(c, "dla_eval_spectra: a quasar has no unmasked pixel in the modelled range");
+    // :169-177: width log-spaced pads each side, 10.^linspace(...)
+    const double lo = log10(umin), hi = log10(umax), ps = pp.pixel_spacing;
+    auto linspace3 = [](double x0, double x1, double* out) {  // numpy/MATLAB linspace(x0, x1, 3)
+      const double step = (x1 - x0) / 2.0;
+      out[0] = x0; out[1] = x0 + step; out[2] = x1;
+    };
+    double e[3];
+    linspace3(lo - 3 * ps, lo - ps, e);
+    for (int t = 0; t < 3; ++t) padded[pad0 + t] = pow(10.0, e[t]);
+    linspace3(hi + ps, hi + 3 * ps, e);
+    for (int t = 0; t < 3; ++t) padded.push_back(pow(10.0, e[t]));
+    // :160-161, set_parameters.m:66-73 (on the kept wavelengths)
+    maxz[(size_t)q] = (kmax / pp.lya_wavelength - 1) - pp.max_z_cut;
+    minz[(size_t)q] = std::max(kmin / pp.lya_wavelength - 1,
+                               pp.lyman_limit * (1 + z_qso[q]) / pp.lya_wavelength - 1 + pp.min_z_cut);
+    pix_ptr[(size_t)q + 1] = pix_ptr[(size_t)q] + n;
+    pad_ptr[(size_t)q + 1] = pad_ptr[(size_t)q] + n_full + 6;
+  }
+  c->dev_prep = true;
+  // mu / omega2 / M are produced on the device: any non-NULL pointer satisfies the planner
+  const double* dummy = fk.data();
+  int rc = plan_batch(c, Q, pix_ptr.data(), pad_ptr.data(), padded.data(), pidx.data(), fk.data(), dummy, dummy, nk.data(),
+                      dummy, minz.data(), maxz.data(), log_prior_dla, log_prior_no_dla);
+  if (rc == DLA_OK) {
+    c->hin.lamk = lamk.data();
+    c->hin.zq = z_qso;
+    cudaError_t e1 = c->d_lamk.ensure(std::max<size_t>(lamk.size() * 8, 32));
+    cudaError_t e2 = c->d_zq.ensure(std::max<size_t>((size_t)Q * 8, 32));
+    if (e1 != cudaSuccess || e2 != cudaSuccess) {
+      c->err = "dla_eval_spectra: device allocation failed";
+      rc = DLA_ERR_OOM;
+    }
+  }
+  if (rc == DLA_OK)
+    rc = run_pipelined(c, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
+  c->dev_prep = false;
+  c->staged = false;  // the staged-run API needs host-prepared inputs
+  if (rc != DLA_OK) return rc;
+  if (min_z_out) memcpy(min_z_out, minz.data(), (size_t)Q * 8);
+  if (max_z_out) memcpy(max_z_out, maxz.data(), (size_t)Q * 8);
   return DLA_OK;
 }
 

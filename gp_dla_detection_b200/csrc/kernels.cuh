@@ -1319,6 +1319,60 @@ chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_
 }
 
 // ----------------------------------------------------------------------------------------------
+// Kp: per-quasar model preparation on the device (process_qsos.m:102, :118-120, :139-147).
+// One thread per kept pixel: rest wavelength, position in the model grid (binary search, as
+// griddedInterpolant / np.interp on a 1-D grid), linear interpolation of mu, the k columns of M
+// and log_omega with the reference's operation order (slope * (x - x0) + f0, no FMA contraction),
+// omega^2 = exp(2 log_omega) * (1 - exp(-tau_0 (1 + z_lya)^beta) + c_0)^2.
+// ----------------------------------------------------------------------------------------------
+struct PrepConsts {
+  double lya_wavelength, c_0, tau_0, beta;
+};
+
+__device__ __forceinline__ double interp_lin(const double* __restrict__ fp, int j, double slope_den_inv_unused,
+                                             double dx, double den) {
+  const double f0 = fp[j], f1 = fp[j + 1];
+  const double slope = __ddiv_rn(__dsub_rn(f1, f0), den);
+  return __dadd_rn(__dmul_rn(slope, dx), f0);
+}
+
+__global__ void __launch_bounds__(128)
+prep_model_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ z_qso,
+                  const double* __restrict__ kept_wavelengths, int n_rest, const double* __restrict__ xp,
+                  const double* __restrict__ m_mu, const double* __restrict__ m_M,
+                  const double* __restrict__ m_log_omega, PrepConsts pc, int k, double* __restrict__ mu,
+                  double* __restrict__ omega2, double* __restrict__ M) {
+  const QuasarDesc d = desc[q0 + blockIdx.y];
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= d.n) return;
+  const int64_t g = d.pix_off + p;
+  const double lam = kept_wavelengths[g];
+  const double x = __ddiv_rn(lam, __dadd_rn(1.0, z_qso[q0 + blockIdx.y]));  // set_parameters.m:14-15
+  // largest j with xp[j] <= x, clamped to [0, n_rest - 2]
+  int lo = 0, hi = n_rest - 1;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (xp[mid] <= x) lo = mid; else hi = mid;
+  }
+  const int j = lo;
+  const bool at_end = x >= xp[n_rest - 1], below = x < xp[0];
+  const double den = __dsub_rn(xp[j + 1], xp[j]);
+  const double dx = __dsub_rn(x, xp[j]);
+  auto val = [&](const double* fp) {
+    if (at_end) return fp[n_rest - 1];
+    if (below) return fp[0];
+    return interp_lin(fp, j, 0.0, dx, den);
+  };
+  mu[g] = val(m_mu);                                                     // :139
+  const double log_omega = val(m_log_omega);                             // :142
+  const double zl = __ddiv_rn(__dsub_rn(lam, pc.lya_wavelength), pc.lya_wavelength);  // :118-120
+  const double sc = __dadd_rn(__dsub_rn(1.0, exp(-pc.tau_0 * pow(__dadd_rn(1.0, zl), pc.beta))), pc.c_0);  // :145
+  omega2[g] = __dmul_rn(exp(2.0 * log_omega), __dmul_rn(sc, sc));        // :143, :147
+  double* Mq = M + (int64_t)k * d.pix_off;                               // column-major n x k
+  for (int c = 0; c < k; ++c) Mq[(int64_t)c * d.n + p] = val(m_M + (int64_t)c * n_rest);  // :140
+}
+
+// ----------------------------------------------------------------------------------------------
 // K3: per quasar log-mean-exp over samples, first-index argmax, posteriors.
 // process_qsos.m:202-212, :223-229; generate_ascii_catalog.m:73 (nanmax, first maximum wins).
 // ----------------------------------------------------------------------------------------------

@@ -170,6 +170,27 @@ class PackedBatch:
                                       self.min_z_dla, self.max_z_dla)) + 16 * self.Q
 
 
+class PackedSpectra:
+    """Ragged raw spectra (all_wavelengths / all_flux / all_noise_variance / all_pixel_mask of
+    preloaded_qsos.mat, preload_qsos.m:73-79) packed for dla_eval_spectra."""
+
+    def __init__(self, all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, z_qsos):
+        Q = len(all_wavelengths)
+        self.Q = Q
+        lens = np.array([len(w) for w in all_wavelengths], dtype=np.int64)
+        self.spec_ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+        cat = lambda xs, dt: (np.ascontiguousarray(np.concatenate([np.asarray(x) for x in xs]), dtype=dt) if Q else np.zeros(0, dt))
+        self.wavelengths = cat(all_wavelengths, np.float64)
+        self.flux = cat(all_flux, np.float64)
+        self.noise_variance = cat(all_noise_variance, np.float64)
+        self.pixel_mask = cat(all_pixel_mask, np.uint8)
+        self.z_qso = np.ascontiguousarray(z_qsos, dtype=np.float64)
+
+    def input_bytes(self) -> int:
+        return sum(a.nbytes for a in (self.spec_ptr, self.wavelengths, self.flux, self.noise_variance,
+                                      self.pixel_mask, self.z_qso))
+
+
 class DlaContext:
     """One ``dla_ctx`` (one CUDA device).  Thin, explicit wrapper of the C ABI."""
 
@@ -267,6 +288,43 @@ class DlaContext:
         del keep
         return out
 
+    def set_model(self, model: LearnedModel, params: Parameters = DEFAULT):
+        """dla_set_model: the learned null model stays resident on the device (process_qsos.m:30-35, :84-86)."""
+        if model.M.shape[1] != self.k:
+            raise ValueError("model rank differs from the context's k")
+        rest = np.ascontiguousarray(model.rest_wavelengths, dtype=np.float64)
+        mu = np.ascontiguousarray(model.mu, dtype=np.float64)
+        lo = np.ascontiguousarray(model.log_omega, dtype=np.float64)
+        Mf = np.ascontiguousarray(np.asfortranarray(np.asarray(model.M, dtype=np.float64)).ravel(order="F"))
+        pp = _lib.dla_prep_params(params.min_lambda, params.max_lambda, params.lya_wavelength, params.lyman_limit,
+                                  params.max_z_cut, params.min_z_cut, params.pixel_spacing, int(params.width), 0,
+                                  float(model.log_c_0), float(model.log_tau_0), float(model.log_beta))
+        d = C.c_double
+        self._check(self._lib.dla_set_model(self._ctx, rest.shape[0], _lib.ptr(rest, d), _lib.ptr(mu, d),
+                                            _lib.ptr(Mf, d), _lib.ptr(lo, d), C.byref(pp)))
+
+    def eval_spectra(self, spectra: "PackedSpectra", log_prior_dla, log_prior_no_dla, mask_gather: str = "reference",
+                     outputs=None):
+        """dla_eval_spectra: raw ragged spectra in (preloaded_qsos.mat arrays), results out; the per-quasar
+        preparation of process_qsos.m:102-180 runs inside the library (selection on the host, model
+        interpolation on the device)."""
+        Q = spectra.Q
+        lpd = np.ascontiguousarray(np.broadcast_to(np.asarray(log_prior_dla, dtype=np.float64), (Q,)))
+        lpn = np.ascontiguousarray(np.broadcast_to(np.asarray(log_prior_no_dla, dtype=np.float64), (Q,)))
+        if outputs is None:
+            outputs = self._alloc_outputs(Q)
+        out, out_args = outputs
+        min_z, max_z = np.full(Q, np.nan), np.full(Q, np.nan)
+        d = C.c_double
+        self._check(self._lib.dla_eval_spectra(
+            self._ctx, Q, _lib.ptr(spectra.spec_ptr, C.c_int64), _lib.ptr(spectra.wavelengths, d),
+            _lib.ptr(spectra.flux, d), _lib.ptr(spectra.noise_variance, d), _lib.ptr(spectra.pixel_mask, C.c_uint8),
+            _lib.ptr(spectra.z_qso, d), _lib.ptr(lpd, d), _lib.ptr(lpn, d),
+            {"reference": 0, "intended": 1}[mask_gather], *out_args, _lib.ptr(min_z, d), _lib.ptr(max_z, d)))
+        out = dict(out)
+        out["min_z_dlas"], out["max_z_dlas"] = min_z, max_z
+        return out
+
     def stage(self, batch: PackedBatch, log_prior_dla, log_prior_no_dla):
         in_args, keep = self._input_args(batch, log_prior_dla, log_prior_no_dla)
         self._check(self._lib.dla_stage_batch(self._ctx, *in_args))
@@ -337,7 +395,7 @@ def finish_outputs(out: dict, batch: PackedBatch, samples: DLASamples, log_prior
 def process_qsos(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, z_qsos, model: LearnedModel,
                  samples: DLASamples, log_priors_dla, log_priors_no_dla, params: Parameters = DEFAULT,
                  device: int = 0, mask_gather: str = "reference", store_sample_ll: bool = True,
-                 context: DlaContext | None = None) -> dict:
+                 context: DlaContext | None = None, device_prep: bool = False) -> dict:
     """Drop-in for the body of process_qsos.m:88-232 over a list of quasars.
 
     Inputs are the per-quasar ragged arrays of preloaded_qsos.mat (preload_qsos.m:73-79) and
@@ -346,6 +404,24 @@ def process_qsos(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, 
     """
     k = model.M.shape[1]
     S = samples.offset_samples.shape[0]
+    if device_prep:
+        # process_qsos.m:102-180 inside the library (dla_set_model + dla_eval_spectra)
+        spectra = PackedSpectra(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, z_qsos)
+        own = context is None
+        ctx = context or DlaContext(k=k, num_lines=params.num_lines, num_samples=S, device=device,
+                                    store_sample_ll=store_sample_ll)
+        try:
+            if own:
+                ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+            ctx.set_model(model, params)
+            out = ctx.eval_spectra(spectra, log_priors_dla, log_priors_no_dla, mask_gather)
+        finally:
+            if own:
+                ctx.close()
+
+        class _Z:  # what finish_outputs reads from a PackedBatch
+            Q, min_z_dla, max_z_dla = spectra.Q, out["min_z_dlas"], out["max_z_dlas"]
+        return finish_outputs(out, _Z, samples, log_priors_dla, log_priors_no_dla)
     prepared = [prepare_quasar(w, f, v, m, z, model, params, mask_gather)
                 for w, f, v, m, z in zip(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, z_qsos)]
     batch = PackedBatch(prepared, k)

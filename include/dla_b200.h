@@ -124,6 +124,44 @@ int dla_fetch_staged(dla_ctx *ctx, double *sample_ll, double *ll_no_dla, double 
                      double *log_post_no_dla, double *log_post_dla,
                      double *model_posteriors, int32_t *map_index);
 
+/* ---- per-quasar preparation on the device -------------------------------
+ * dla_set_model + dla_eval_spectra replace process_qsos.m:102-120 (rest-frame cut, pixel
+ * mask), :139-147 (linear interpolation of mu / M / log_omega onto the spectrum, omega^2
+ * scaling), :160-161 (z_DLA range), :169-180 (padded grid, gather index) AND everything
+ * dla_eval_batch replaces, from the raw ragged arrays of preloaded_qsos.mat
+ * (preload_qsos.m:73-79).  Selection, counts and the padded grid are one cheap host pass
+ * inside the library; the interpolation of the n x (k+2) model values, exp and scaling run
+ * in a CUDA kernel, so the learned model is uploaded once and per quasar only the kept
+ * wavelengths, flux and noise variance cross PCIe. */
+typedef struct {
+  double min_lambda, max_lambda;      /* set_parameters.m:33-34 */
+  double lya_wavelength, lyman_limit; /* :5, :7 */
+  double max_z_cut, min_z_cut;        /* :65, :69  kms_to_z(3000) */
+  double pixel_spacing;               /* :60 */
+  int32_t width;                      /* :59 (must be 3: voigt.c:229) */
+  int32_t reserved;
+  double log_c_0, log_tau_0, log_beta; /* learned_qso_model: process_qsos.m:84-86 */
+} dla_prep_params;
+
+/* learned_qso_model_*.mat (learn_qso_model.m:113-123): rest_wavelengths [n_rest] strictly
+ * increasing, mu [n_rest], M [n_rest x k] COLUMN-major, log_omega [n_rest]. */
+int dla_set_model(dla_ctx *ctx, int64_t n_rest, const double *rest_wavelengths, const double *mu,
+                  const double *M, const double *log_omega, const dla_prep_params *prep);
+
+/* Q raw spectra, ragged: spec_ptr [Q+1] offsets into wavelengths / flux / noise_variance /
+ * pixel_mask (1 = masked), z_qso [Q].  mask_gather: 0 = the gather as written in the
+ * reference (process_qsos.m:180/:189: first n profile elements), 1 = the unmasked positions.
+ * Outputs as dla_eval_batch, plus min_z_dla / max_z_dla [Q] (process_qsos.m:160-161; may be
+ * NULL).  A quasar with no unmasked pixel in the modelled range is DLA_ERR_BAD_ARG. */
+int dla_eval_spectra(dla_ctx *ctx, int64_t Q, const int64_t *spec_ptr, const double *wavelengths,
+                     const double *flux, const double *noise_variance, const uint8_t *pixel_mask,
+                     const double *z_qso, const double *log_prior_dla, const double *log_prior_no_dla,
+                     int32_t mask_gather,
+                     double *sample_ll, double *ll_no_dla, double *ll_dla,
+                     double *log_post_no_dla, double *log_post_dla,
+                     double *model_posteriors, int32_t *map_index,
+                     double *min_z_dla, double *max_z_dla);
+
 int dla_get_timing(const dla_ctx *ctx, dla_timing *out);
 
 /* Unit seams (one call = one reference call; for parity tests and for running

@@ -177,3 +177,24 @@ def test_gpu_against_committed_goldens():
         got = _run_gpu(prepared, samples, k, S, sp.log_priors_dla, sp.log_priors_no_dla)
         ref = {key[len(pre):]: G[key] for key in G.files if key.startswith(pre) and key != pre + "checksum"}
         assert_parity(got, ref)
+
+
+@pytest.mark.parametrize("cfg,mask_gather", [("tiny", "reference"), ("config1", "reference"),
+                                             ("config3", "reference"), ("config3", "intended")])
+def test_device_side_preparation_matches_host_preparation(oracle, cfg, mask_gather):
+    """dla_set_model + dla_eval_spectra (process_qsos.m:102-180 inside the library: selection on the
+    host, interpolation / omega^2 scaling in a CUDA kernel) against the numpy preparation + dla_eval_batch
+    and against the oracle on the numpy-prepared inputs."""
+    Q, S = (4, 64) if cfg == "tiny" else (5, 128)
+    params, model, samples, sp, prepared = prepared_config(cfg, Q, S, mask_gather)
+    a = process_qsos(sp.all_wavelengths, sp.all_flux, sp.all_noise_variance, sp.all_pixel_mask, sp.z_qsos, model,
+                     samples, sp.log_priors_dla, sp.log_priors_no_dla, params, mask_gather=mask_gather)
+    b = process_qsos(sp.all_wavelengths, sp.all_flux, sp.all_noise_variance, sp.all_pixel_mask, sp.z_qsos, model,
+                     samples, sp.log_priors_dla, sp.log_priors_no_dla, params, mask_gather=mask_gather,
+                     device_prep=True)
+    assert np.array_equal(a["min_z_dlas"], b["min_z_dlas"]) and np.array_equal(a["max_z_dlas"], b["max_z_dlas"])
+    assert_parity(b, a)
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(b, ref)
+    rel = np.abs(a["sample_log_likelihoods_dla"] - b["sample_log_likelihoods_dla"]) / np.abs(a["sample_log_likelihoods_dla"])
+    print(cfg, mask_gather, "device prep vs host prep, worst rel", rel.max())

@@ -40,7 +40,7 @@ def test_no_cpu_fallback_create_fails_loudly_without_a_device():
 def test_create_rejects_bad_parameters():
     lib = _lib.load()
     ctx = C.c_void_p()
-    for k, nl in [(0, 3), (21, 3), (20, 0), (20, 32)]:
+    for k, nl in [(0, 3), (65, 3), (20, 0), (20, 32)]:  # k: 1..20 fused, 21..64 column-block path
         p = _lib.dla_params(k, nl, 10, 1, 0, 0)
         assert lib.dla_create(C.byref(ctx), 0, C.byref(p)) == -1
         assert lib.dla_last_error(None)
