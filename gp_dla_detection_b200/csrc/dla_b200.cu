@@ -41,6 +41,29 @@ struct DevBuf {
   T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// grow-only page-locked host buffer (staging for arrays the library builds itself)
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    const size_t want = bytes + bytes / 4;
+    cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
 struct Chunk {
   int q0, nq;
   int64_t wu_doubles, bmat_doubles;
@@ -80,6 +103,7 @@ struct dla_ctx {
   int64_t n_rest = 0;
   dla_prep_params prep{};
   DevBuf d_mrest, d_mmu, d_mM, d_mlo, d_lamk, d_zq;
+  PinBuf h_lamk, h_fk, h_nk, h_padded, h_pidx;  // dla_eval_spectra's compacted arrays (page-locked: async H2D)
   // hypothesis set
   // (sorted by offset once: the hypotheses of a warp are then neighbours in z; d_perm maps a
   //  sorted position back to the caller's sample index)
@@ -423,6 +447,7 @@ void dla_destroy(dla_ctx* c) {
     b->release();
   for (auto& ev : c->ev)
     if (ev) cudaEventDestroy(ev);
+  for (PinBuf* b : {&c->h_lamk, &c->h_fk, &c->h_nk, &c->h_padded, &c->h_pidx}) b->release();
   for (auto& ev : c->ev_time) cudaEventDestroy(ev);
   for (auto& ev : c->ev_sync) cudaEventDestroy(ev);
   if (c->s_in) cudaStreamDestroy(c->s_in);
@@ -825,28 +850,37 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
   const dla_prep_params& pp = c->prep;
   // one host pass per quasar: process_qsos.m:102-116 (selection), :160-161 (z range), :169-180 (padded grid, gather)
   std::vector<int64_t> pix_ptr((size_t)Q + 1, 0), pad_ptr((size_t)Q + 1, 0);
-  std::vector<double> lamk, fk, nk, padded, minz((size_t)Q), maxz((size_t)Q);
-  std::vector<int32_t> pidx;
+  std::vector<double> minz((size_t)Q), maxz((size_t)Q);
   const int64_t ntot = spec_ptr[Q] - spec_ptr[0];
-  lamk.reserve((size_t)ntot); fk.reserve((size_t)ntot); nk.reserve((size_t)ntot); pidx.reserve((size_t)ntot);
-  padded.reserve((size_t)ntot + 6 * (size_t)Q);
+  if (ntot < 0) BAD_ARG(c, "dla_eval_spectra: spec_ptr must be non-decreasing");
+  CU_TRY(c, cudaSetDevice(c->device));
+  CU_TRY(c, c->h_lamk.ensure((size_t)ntot * 8 + 64));
+  CU_TRY(c, c->h_fk.ensure((size_t)ntot * 8 + 64));
+  CU_TRY(c, c->h_nk.ensure((size_t)ntot * 8 + 64));
+  CU_TRY(c, c->h_pidx.ensure((size_t)ntot * 4 + 64));
+  CU_TRY(c, c->h_padded.ensure(((size_t)ntot + 6 * (size_t)Q) * 8 + 64));
+  double *lamk = c->h_lamk.as<double>(), *fk = c->h_fk.as<double>(), *nk = c->h_nk.as<double>();
+  double* padded = c->h_padded.as<double>();
+  int32_t* pidx = c->h_pidx.as<int32_t>();
+  int64_t nkept = 0, npadded = 0;
   for (int64_t q = 0; q < Q; ++q) {
     const int64_t a = spec_ptr[q], b = spec_ptr[q + 1];
     if (b < a) BAD_ARG(c, "dla_eval_spectra: spec_ptr must be non-decreasing");
     const double opz = 1.0 + z_qso[q];
-    const size_t pad0 = padded.size();
-    padded.resize(pad0 + 3);  // left pads, filled below
+    const int64_t pad0 = npadded;
+    npadded += 3;  // left pads, filled below
     int64_t n_full = 0, n = 0;
     double umin = INFINITY, umax = -INFINITY, kmin = INFINITY, kmax = -INFINITY;
     for (int64_t i = a; i < b; ++i) {
-      const double rest = wavelengths[i] / opz;                              // :102, set_parameters.m:14-15
-      if (!(rest >= pp.min_lambda && rest <= pp.max_lambda)) continue;        // :104-105
       const double w = wavelengths[i];
-      padded.push_back(w);                                                    // :109 this_unmasked_wavelengths
+      const double rest = w / opz;                                            // :102, set_parameters.m:14-15
+      if (!(rest >= pp.min_lambda && rest <= pp.max_lambda)) continue;        // :104-105
+      padded[npadded++] = w;                                                  // :109 this_unmasked_wavelengths
       umin = std::min(umin, w); umax = std::max(umax, w);
       if (!pixel_mask[i]) {                                                   // :111-116
-        lamk.push_back(w); fk.push_back(flux[i]); nk.push_back(noise_variance[i]);
-        pidx.push_back((int32_t)(mask_gather ? n_full : n));                  // :180/:189 as written, or the unmasked positions
+        lamk[nkept] = w; fk[nkept] = flux[i]; nk[nkept] = noise_variance[i];
+        pidx[nkept] = (int32_t)(mask_gather ? n_full : n);                    // :180/:189 as written, or the unmasked positions
+        ++nkept;
         kmin = std::min(kmin, w); kmax = std::max(kmax, w);
         ++n;
       }
@@ -863,7 +897,7 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
     linspace3(lo - 3 * ps, lo - ps, e);
     for (int t = 0; t < 3; ++t) padded[pad0 + t] = pow(10.0, e[t]);
     linspace3(hi + ps, hi + 3 * ps, e);
-    for (int t = 0; t < 3; ++t) padded.push_back(pow(10.0, e[t]));
+    for (int t = 0; t < 3; ++t) padded[npadded++] = pow(10.0, e[t]);
     // :160-161, set_parameters.m:66-73 (on the kept wavelengths)
     maxz[(size_t)q] = (kmax / pp.lya_wavelength - 1) - pp.max_z_cut;
     minz[(size_t)q] = std::max(kmin / pp.lya_wavelength - 1,
@@ -873,13 +907,13 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
   }
   c->dev_prep = true;
   // mu / omega2 / M are produced on the device: any non-NULL pointer satisfies the planner
-  const double* dummy = fk.data();
-  int rc = plan_batch(c, Q, pix_ptr.data(), pad_ptr.data(), padded.data(), pidx.data(), fk.data(), dummy, dummy, nk.data(),
+  const double* dummy = fk;
+  int rc = plan_batch(c, Q, pix_ptr.data(), pad_ptr.data(), padded, pidx, fk, dummy, dummy, nk,
                       dummy, minz.data(), maxz.data(), log_prior_dla, log_prior_no_dla);
   if (rc == DLA_OK) {
-    c->hin.lamk = lamk.data();
+    c->hin.lamk = lamk;
     c->hin.zq = z_qso;
-    cudaError_t e1 = c->d_lamk.ensure(std::max<size_t>(lamk.size() * 8, 32));
+    cudaError_t e1 = c->d_lamk.ensure(std::max<size_t>((size_t)nkept * 8, 32));
     cudaError_t e2 = c->d_zq.ensure(std::max<size_t>((size_t)Q * 8, 32));
     if (e1 != cudaSuccess || e2 != cudaSuccess) {
       c->err = "dla_eval_spectra: device allocation failed";
