@@ -1,0 +1,117 @@
+"""On-disk products either side of the hot path, by the reference's variable names.
+
+  learned_qso_model_<set>.mat  learn_qso_model.m:113-123   -> load_learned_model
+  dla_samples.mat              generate_dla_samples.m:59-63 -> load_dla_samples
+  preloaded_qsos.mat           preload_qsos.m:73-79         -> load_preloaded_qsos
+  processed_qsos_<set>.mat     process_qsos.m:235-249       -> save_processed_qsos / load_processed_qsos
+
+The reference writes MATLAB v7.3 files (= HDF5).  Reading/writing HDF5 needs h5py, which is NOT in
+this image; when it is importable the v7.3 branch is used (datasets are stored transposed, ragged cell
+arrays as object references: the conventions CDDF_analysis/calc_cddf.py:59-124 relies on).  Without
+h5py the same variables are exchanged as MATLAB v5/v7 files through scipy.io (both MATLAB and Octave
+load them with a plain ``load``), which is also what the tests exercise here.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .process_qsos import DLASamples, LearnedModel
+
+RESULT_VARIABLES = ("min_z_dlas", "max_z_dlas", "log_priors_no_dla", "log_priors_dla", "log_likelihoods_no_dla",
+                    "sample_log_likelihoods_dla", "log_likelihoods_dla", "log_posteriors_no_dla", "log_posteriors_dla",
+                    "model_posteriors", "p_no_dlas", "p_dlas")  # process_qsos.m:235-243
+
+
+def _is_hdf5(path: str) -> bool:
+    with open(path, "rb") as f:
+        head = f.read(512 + 8)
+    return head[:8] == b"\x89HDF\r\n\x1a\n" or head[512:520] == b"\x89HDF\r\n\x1a\n"
+
+
+def _h5py():
+    try:
+        import h5py  # noqa: F401
+        return h5py
+    except ImportError as e:
+        raise ImportError("this file is MATLAB v7.3 (HDF5); reading it needs h5py, which is not installed. "
+                          "Re-save it from MATLAB/Octave with `save -v7 ...` or install h5py.") from e
+
+
+def _load(path: str, names) -> dict:
+    """name -> ndarray (numeric) or list of 1-D ndarrays (cell array of vectors), MATLAB orientation."""
+    if _is_hdf5(path):
+        h5py = _h5py()
+        out = {}
+        with h5py.File(path, "r") as f:
+            for n in names:
+                ds = f[n]
+                if ds.dtype == object:   # cell array: references to the per-quasar vectors
+                    out[n] = [np.asarray(f[r]).ravel() for r in np.asarray(ds).ravel()]
+                else:
+                    out[n] = np.asarray(ds).T  # HDF5 stores MATLAB arrays transposed
+        return out
+    from scipy.io import loadmat
+    raw = loadmat(path, variable_names=list(names))
+    out = {}
+    for n in names:
+        v = raw[n]
+        if v.dtype == object:
+            out[n] = [np.asarray(x).ravel() for x in v.ravel()]
+        else:
+            out[n] = np.asarray(v)
+    return out
+
+
+def load_learned_model(path: str) -> LearnedModel:
+    v = _load(path, ("rest_wavelengths", "mu", "M", "log_omega", "log_c_0", "log_tau_0", "log_beta"))  # process_qsos.m:30-35
+    rest = np.asarray(v["rest_wavelengths"], dtype=np.float64).ravel()
+    M = np.asarray(v["M"], dtype=np.float64)
+    if M.shape[0] != rest.shape[0]:
+        M = M.T
+    return LearnedModel(rest, np.asarray(v["mu"], dtype=np.float64).ravel(), np.asfortranarray(M),
+                        np.asarray(v["log_omega"], dtype=np.float64).ravel(), float(np.ravel(v["log_c_0"])[0]),
+                        float(np.ravel(v["log_tau_0"])[0]), float(np.ravel(v["log_beta"])[0]))
+
+
+def load_dla_samples(path: str) -> DLASamples:
+    v = _load(path, ("offset_samples", "log_nhi_samples", "nhi_samples"))                # process_qsos.m:37-40
+    return DLASamples(*(np.asarray(v[n], dtype=np.float64).ravel() for n in ("offset_samples", "log_nhi_samples", "nhi_samples")))
+
+
+def load_preloaded_qsos(path: str) -> dict:
+    """all_wavelengths / all_flux / all_noise_variance / all_pixel_mask as lists of 1-D arrays (process_qsos.m:42-50)."""
+    v = _load(path, ("all_wavelengths", "all_flux", "all_noise_variance", "all_pixel_mask"))
+    v["all_pixel_mask"] = [np.asarray(m).astype(bool) for m in v["all_pixel_mask"]]
+    return v
+
+
+def save_processed_qsos(path: str, results: dict, extra: dict | None = None, v73: bool = False) -> None:
+    """processed_qsos_<set>.mat with the variables of process_qsos.m:235-243 (column vectors, [Q x S]
+    sample matrix, [Q x 2] posteriors).  ``extra``: the bookkeeping variables of :235-238 (release names,
+    test_ind, ...).  v73=True writes HDF5 with MATLAB's transposed layout (needs h5py)."""
+    vars_ = {}
+    for n in RESULT_VARIABLES:
+        if results.get(n) is None:
+            continue
+        a = np.asarray(results[n], dtype=np.float64)
+        vars_[n] = a.reshape(-1, 1) if a.ndim == 1 else a
+    for n, a in (extra or {}).items():
+        vars_[n] = a
+    if v73:
+        h5py = _h5py()
+        with h5py.File(path, "w", userblock_size=512) as f:
+            for n, a in vars_.items():
+                f.create_dataset(n, data=np.asarray(a).T)
+        with open(path, "r+b") as f:  # the v7.3 text header MATLAB looks for
+            f.write(b"MATLAB 7.3 MAT-file, Platform: gp_dla_detection_b200".ljust(124) + b"\x00\x02IM")
+        return
+    from scipy.io import savemat
+    savemat(path, vars_, do_compression=False, oned_as="column")
+
+
+def load_processed_qsos(path: str) -> dict:
+    v = _load(path, RESULT_VARIABLES)
+    for n in RESULT_VARIABLES:
+        if n not in ("sample_log_likelihoods_dla", "model_posteriors"):
+            v[n] = np.asarray(v[n]).ravel()
+    return v
