@@ -19,6 +19,7 @@ EXPORTED_SYMBOLS = (
     "dla_abi_version", "dla_device_count", "dla_create", "dla_destroy", "dla_last_error",
     "dla_set_samples", "dla_eval_batch", "dla_stage_batch", "dla_run_staged", "dla_fetch_staged",
     "dla_get_timing", "dla_voigt", "dla_log_mvnpdf_low_rank", "dla_set_model", "dla_eval_spectra",
+    "dla_train_set_data", "dla_train_objective",
 )
 
 
@@ -102,6 +103,10 @@ def load() -> C.CDLL:
     lib.dla_eval_spectra.restype = C.c_int
     lib.dla_eval_spectra.argtypes = ([_ctx, C.c_int64, _pi64, _pd, _pd, _pd, C.POINTER(C.c_uint8), _pd, _pd, _pd, C.c_int32]
                                      + _OUTPUTS + [_pd, _pd])
+    lib.dla_train_set_data.restype = C.c_int
+    lib.dla_train_set_data.argtypes = [_ctx, C.c_int64, C.c_int64, _pd, _pd, _pd]
+    lib.dla_train_objective.restype = C.c_int
+    lib.dla_train_objective.argtypes = [_ctx, _pd, C.c_int32, _pd, _pd]
     _lib = lib
     return lib
 

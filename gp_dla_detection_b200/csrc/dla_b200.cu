@@ -103,7 +103,10 @@ struct dla_ctx {
   int64_t n_rest = 0;
   dla_prep_params prep{};
   DevBuf d_mrest, d_mmu, d_mM, d_mlo, d_lamk, d_zq;
-  PinBuf h_lamk, h_fk, h_nk, h_padded, h_pidx;  // dla_eval_spectra's compacted arrays (page-locked: async H2D)
+  PinBuf h_lamk, h_fk, h_nk, h_padded, h_pidx;
+  // training objective (dla_train_set_data / dla_train_objective)
+  int64_t tQ = 0, tN = 0;
+  DevBuf t_y, t_l, t_nv, t_x, t_om2, t_aux, t_E, t_fq, t_beta, t_P, t_A1, t_S, t_gp, t_g, t_gsc, t_desc;  // dla_eval_spectra's compacted arrays (page-locked: async H2D)
   // hypothesis set
   // (sorted by offset once: the hypotheses of a warp are then neighbours in z; d_perm maps a
   //  sorted position back to the caller's sample index)
@@ -427,6 +430,9 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
                                   (int)dla::K2P_SMEM_BYTES));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
+  CREATE_TRY(cudaFuncSetAttribute(dla::train_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  dla::TRC_WARPS * ((dla::TRAIN_KMAX + 1) * (dla::TRAIN_KMAX + 2) +
+                                                    dla::TRAIN_KMAX * (dla::TRAIN_KMAX + 1) + dla::TRAIN_KMAX) * 8));
   CREATE_TRY(cudaFuncSetAttribute(dla::chol_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   dla::CHG_WARPS * (dla::KGEN_MAX + 1) * (dla::KGEN_MAX + 2) * 8));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
@@ -443,7 +449,9 @@ void dla_destroy(dla_ctx* c) {
   for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_perm, &c->d_etab256, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
                     &c->d_nv, &c->d_M, &c->d_pix4, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
                     &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk, &c->d_G,
-                    &c->d_mrest, &c->d_mmu, &c->d_mM, &c->d_mlo, &c->d_lamk, &c->d_zq})
+                    &c->d_mrest, &c->d_mmu, &c->d_mM, &c->d_mlo, &c->d_lamk, &c->d_zq,
+                    &c->t_y, &c->t_l, &c->t_nv, &c->t_x, &c->t_om2, &c->t_aux, &c->t_E, &c->t_fq, &c->t_beta, &c->t_P,
+                    &c->t_A1, &c->t_S, &c->t_gp, &c->t_g, &c->t_gsc, &c->t_desc})
     b->release();
   for (auto& ev : c->ev)
     if (ev) cudaEventDestroy(ev);
@@ -927,6 +935,124 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
   if (rc != DLA_OK) return rc;
   if (min_z_out) memcpy(min_z_out, minz.data(), (size_t)Q * 8);
   if (max_z_out) memcpy(max_z_out, maxz.data(), (size_t)Q * 8);
+  return DLA_OK;
+}
+
+int dla_train_set_data(dla_ctx* c, int64_t Q, int64_t n, const double* y, const double* l1pz, const double* nv) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!y || !l1pz || !nv) BAD_ARG(c, "dla_train_set_data: NULL pointer");
+  if (Q < 1 || n < 1 || n > (1 << 20) || Q > (1 << 26)) BAD_ARG(c, "dla_train_set_data: sizes out of range");
+  if (c->p.k > dla::TRAIN_KMAX) BAD_ARG(c, "dla_train_set_data: the training objective supports k <= 32");
+  CU_TRY(c, cudaSetDevice(c->device));
+  const size_t bytes = (size_t)Q * n * 8;
+  CU_TRY(c, c->t_y.ensure(bytes));
+  CU_TRY(c, c->t_l.ensure(bytes));
+  CU_TRY(c, c->t_nv.ensure(bytes));
+  CU_TRY(c, cudaMemcpyAsync(c->t_y.p, y, bytes, cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemcpyAsync(c->t_l.p, l1pz, bytes, cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaMemcpyAsync(c->t_nv.p, nv, bytes, cudaMemcpyHostToDevice, c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  c->tQ = Q;
+  c->tN = n;
+  c->staged = false;  // shares the W/U/G workspace with the evaluation path
+  c->ran = false;
+  return DLA_OK;
+}
+
+int dla_train_objective(dla_ctx* c, const double* x, int32_t apply_priors, double* f, double* g) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!x || !f || !g) BAD_ARG(c, "dla_train_objective: NULL pointer");
+  if (c->tQ == 0) {
+    c->err = "dla_train_objective: dla_train_set_data has not been called";
+    return DLA_ERR_STATE;
+  }
+  CU_TRY(c, cudaSetDevice(c->device));
+  c->staged = false;
+  c->ran = false;
+  const int64_t Q = c->tQ;
+  const int n = (int)c->tN, k = c->p.k;
+  const int T = k * (k + 1) / 2;
+  const int npad = (int)round_up(n, dla::KC);
+  const int nqb = (int)((Q + dla::TS - 1) / dla::TS);
+  const int64_t Qpad = (int64_t)nqb * dla::TS;
+  const ColGeom gen = col_geom(k);
+  const int64_t nx = (int64_t)n * (k + 1) + 3;
+  const int nsplit = (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(32, Q), (600 + (n + 7) / 8 - 1) / ((n + 7) / 8)));
+  cudaStream_t st = c->stream;
+  CU_TRY(c, c->t_x.ensure((size_t)nx * 8));
+  CU_TRY(c, c->t_om2.ensure((size_t)n * 8));
+  CU_TRY(c, c->d_W.ensure((size_t)Qpad * npad * 8));
+  CU_TRY(c, c->d_U.ensure((size_t)Qpad * npad * 8));
+  CU_TRY(c, c->d_bmat.ensure((size_t)npad * gen.ncol * 8));
+  CU_TRY(c, c->d_G.ensure((size_t)Qpad * gen.ncol * 8));
+  CU_TRY(c, c->t_aux.ensure((size_t)3 * dla::TRAIN_NSEG * Qpad * 8));
+  CU_TRY(c, c->t_E.ensure((size_t)dla::TRAIN_NE * Q * n * 8));
+  CU_TRY(c, c->t_fq.ensure((size_t)Q * 8));
+  CU_TRY(c, c->t_beta.ensure((size_t)Q * k * 8));
+  CU_TRY(c, c->t_P.ensure((size_t)Q * T * 8));
+  CU_TRY(c, c->t_A1.ensure((size_t)nsplit * n * k * 8));
+  CU_TRY(c, c->t_S.ensure((size_t)nsplit * n * T * 8));
+  CU_TRY(c, c->t_gp.ensure((size_t)nsplit * n * 4 * 8));
+  CU_TRY(c, c->t_g.ensure((size_t)n * (k + 1) * 8));
+  CU_TRY(c, c->t_gsc.ensure((size_t)n * 3 * 8));
+  CU_TRY(c, c->t_desc.ensure(sizeof(QuasarDesc)));
+  QuasarDesc hd{};
+  hd.n = n;
+  hd.P = n + 6;
+  hd.npad = npad;
+  hd.ident = 1;
+  CU_TRY(c, cudaMemcpyAsync(c->t_desc.p, &hd, sizeof hd, cudaMemcpyHostToDevice, st));
+  CU_TRY(c, cudaMemcpyAsync(c->t_x.p, x, (size_t)nx * 8, cudaMemcpyHostToDevice, st));
+  const double* dx = c->t_x.as<double>();
+  const dla::TrainConsts tc{exp(x[nx - 3]), exp(x[nx - 2]), exp(x[nx - 1])};   // objective.m:30-32
+  dla::train_omega2_kernel<<<(n + 255) / 256, 256, 0, st>>>(dx + (int64_t)n * k, n, c->t_om2.as<double>());
+  dla::train_weights_kernel<<<nqb, dla::TS * dla::TRAIN_NSEG, 0, st>>>(
+      Q, n, npad, c->t_y.as<double>(), c->t_l.as<double>(), c->t_nv.as<double>(), c->t_om2.as<double>(), tc,
+      c->d_W.as<double>(), c->d_U.as<double>(), c->t_aux.as<double>(), c->t_E.as<double>());
+  {
+    dim3 grid((unsigned)(((int64_t)(npad / 4) * gen.ncol + 255) / 256), 1);
+    dla::build_bmat_kernel<<<grid, 256, 0, st>>>(c->t_desc.as<QuasarDesc>(), 0, dx, c->d_bmat.as<double>(), k, gen.ncol, gen.voff);
+  }
+  {
+    const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
+    dim3 grid((unsigned)nqb, (unsigned)gen.nblocks);
+    dla::contract_block_kernel<<<grid, dla::K2_THREADS, smem, st>>>(
+        c->t_desc.as<QuasarDesc>(), 0, nqb, c->d_W.as<double>(), c->d_U.as<double>(), c->d_bmat.as<double>(),
+        c->d_G.as<double>(), gen.ncol, gen.voff / 8, gen.tpw);
+  }
+  {
+    const size_t smem = (size_t)dla::TRC_WARPS * ((k + 1) * (k + 2) + k * (k + 1) + k) * 8;
+    dla::train_chol_kernel<<<(unsigned)((Q + dla::TRC_WARPS - 1) / dla::TRC_WARPS), dla::TRC_WARPS * 32, smem, st>>>(
+        Q, Qpad, c->d_G.as<double>(), c->t_aux.as<double>(), k, gen.ncol, gen.voff, c->t_fq.as<double>(),
+        c->t_beta.as<double>(), c->t_P.as<double>());
+  }
+  {
+    dim3 grid((unsigned)((n + dla::TRG_WARPS - 1) / dla::TRG_WARPS), (unsigned)nsplit);
+    dla::train_grad_kernel<<<grid, dla::TRG_WARPS * 32, 0, st>>>(
+        Q, n, k, dx, c->t_E.as<double>(), c->t_beta.as<double>(), c->t_P.as<double>(), tc, nsplit,
+        c->t_A1.as<double>(), c->t_S.as<double>(), c->t_gp.as<double>());
+  }
+  dla::train_finish_kernel<<<(n * (k + 1) + 255) / 256, 256, 0, st>>>(
+      n, k, nsplit, dx, c->t_A1.as<double>(), c->t_S.as<double>(), c->t_gp.as<double>(), c->t_g.as<double>(),
+      c->t_gsc.as<double>());
+  CU_TRY(c, cudaGetLastError());
+  std::vector<double> fq((size_t)Q), gsc((size_t)n * 3);
+  CU_TRY(c, cudaMemcpyAsync(g, c->t_g.p, (size_t)n * (k + 1) * 8, cudaMemcpyDeviceToHost, st));
+  CU_TRY(c, cudaMemcpyAsync(fq.data(), c->t_fq.p, (size_t)Q * 8, cudaMemcpyDeviceToHost, st));
+  CU_TRY(c, cudaMemcpyAsync(gsc.data(), c->t_gsc.p, (size_t)n * 3 * 8, cudaMemcpyDeviceToHost, st));
+  CU_TRY(c, cudaStreamSynchronize(st));
+  double fs = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+  for (int64_t q = 0; q < Q; ++q) fs += fq[(size_t)q];                       // objective.m:50
+  for (int p = 0; p < n; ++p) { s1 += gsc[(size_t)p * 3]; s2 += gsc[(size_t)p * 3 + 1]; s3 += gsc[(size_t)p * 3 + 2]; }
+  if (apply_priors) {
+    s2 += tc.tau_0 * (tc.tau_0 - 0.0023) / (0.0007 * 0.0007);                 // objective.m:60-64
+    s3 += tc.beta * (tc.beta - 3.65) / (0.21 * 0.21);                         // :67-71
+  }
+  *f = fs;
+  g[nx - 3] = s1;
+  g[nx - 2] = s2;
+  g[nx - 1] = s3;
+  c->timing.launches = 7;
   return DLA_OK;
 }
 

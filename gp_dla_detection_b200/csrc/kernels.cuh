@@ -1373,6 +1373,281 @@ prep_model_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __r
 }
 
 // ----------------------------------------------------------------------------------------------
+// Training objective: objective.m:12-75 over spectrum_loss.m:14-76.
+// The same Woodbury algebra as the hot path with the roles changed: the "samples" of a tile are 64
+// TRAINING QUASARS on the common rest-frame grid, w = 1/d, u = y/d (0 where the flux is NaN), and the
+// contraction [W | U].[Phi | M] (contract_block_kernel, FP64 tensor cores) gives B_q - I and
+// v_q = M' D^-1 y for every quasar.  With P_q = B_q^-1 and beta_q = P_q v_q (train_chol_kernel):
+//   alpha = K^-1 y = (y - M beta) / d,      diag K^-1 = 1/d - (M_p P M_p') / d^2,
+//   K^-1 M = D^-1 M P  (because C M = I - B^-1),   M' alpha = beta,
+// so  dM_p = -sum_q alpha_qp beta_q' + M_p (sum_q P_q / d_qp)  and the other gradients are sums of
+// t_qp = alpha_qp^2 - diag K^-1_qp against per-pixel factors (train_grad_kernel).
+// ----------------------------------------------------------------------------------------------
+constexpr int TRAIN_KMAX = 32;                 // one lane per latent dimension in the gradient kernel
+constexpr int TRAIN_NC = (TRAIN_KMAX * (TRAIN_KMAX + 1) / 2 + 31) / 32;  // vech columns per lane
+constexpr int TRAIN_NSEG = 4;
+constexpr int TRAIN_NE = 6;                    // per-(quasar, pixel) factors kept for the gradient pass
+
+struct TrainConsts {
+  double c_0, tau_0, beta;
+};
+
+__global__ void train_omega2_kernel(const double* __restrict__ log_omega, int n, double* __restrict__ omega2) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < n) omega2[p] = exp(2.0 * log_omega[p]);   // objective.m:29
+}
+
+// spectrum_loss.m:22-33: one lane per quasar walks a quarter of the grid.
+// E[0] 1/d (0 if missing), E[1] y (0 if missing), E[2] omega2 * scaling, E[3] scaling,
+// E[4] optical depth * absorption, E[5] beta * log(1 + z_lya)
+__global__ void __launch_bounds__(TS * TRAIN_NSEG)
+train_weights_kernel(int64_t Q, int n, int npad, const double* __restrict__ y, const double* __restrict__ l1pz,
+                     const double* __restrict__ nv, const double* __restrict__ omega2, TrainConsts tc,
+                     double* __restrict__ Wbuf, double* __restrict__ Ubuf, double* __restrict__ aux /* [3 NSEG][Qpad] */,
+                     double* __restrict__ E /* [6][Q][n] */) {
+  const int tid = threadIdx.x, qi = tid & (TS - 1), seg = tid / TS;
+  const int64_t q = (int64_t)blockIdx.x * TS + qi;
+  const int64_t Qpad = (int64_t)gridDim.x * TS;
+  const int npc = npad >> 2;
+  const int g0 = (int)(((int64_t)seg * npc) / TRAIN_NSEG), g1 = (int)(((int64_t)(seg + 1) * npc) / TRAIN_NSEG);
+  double* wp = Wbuf + ((int64_t)blockIdx.x * npc + g0) * (TS * 4) + qi * 4;
+  double* up = Ubuf + ((int64_t)blockIdx.x * npc + g0) * (TS * 4) + qi * 4;
+  double q0acc = 0.0, ldacc = 0.0, cnt = 0.0;
+  for (int g = g0; g < g1; ++g, wp += TS * 4, up += TS * 4) {
+    double w[4], u[4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      const int p = 4 * g + h;
+      w[h] = 0.0;
+      u[h] = 0.0;
+      if (q < Q && p < n) {
+        const int64_t e = q * n + p;
+        const double yy = y[e], lz = l1pz[e];
+        const bool ok = (yy == yy);                                   // objective.m:42 ind = ~isnan(flux)
+        const double od = tc.tau_0 * pow(lz, tc.beta);                // spectrum_loss.m:22
+        const double ab = exp(-od);                                   // :23
+        const double sf = 1.0 - ab + tc.c_0;                          // :26
+        const double osf = omega2[p] * sf;
+        const double d = nv[e] + osf * sf;                            // :27, :29
+        const double dinv = ok ? 1.0 / d : 0.0;                       // :31
+        const double y0 = ok ? yy : 0.0;
+        const int64_t QN = Q * n;
+        E[e] = dinv; E[QN + e] = y0; E[2 * QN + e] = ok ? osf : 0.0; E[3 * QN + e] = ok ? sf : 0.0;
+        E[4 * QN + e] = ok ? od * ab : 0.0; E[5 * QN + e] = ok ? tc.beta * log(lz) : 0.0;
+        if (ok) {
+          w[h] = dinv;
+          u[h] = dinv * y0;                                           // :32
+          q0acc = fma(y0, u[h], q0acc);
+          ldacc += log(d);                                            // :48
+          cnt += 1.0;
+        }
+      }
+    }
+    reinterpret_cast<double2*>(wp)[0] = make_double2(w[0], w[1]);
+    reinterpret_cast<double2*>(wp)[1] = make_double2(w[2], w[3]);
+    reinterpret_cast<double2*>(up)[0] = make_double2(u[0], u[1]);
+    reinterpret_cast<double2*>(up)[1] = make_double2(u[2], u[3]);
+  }
+  aux[(int64_t)seg * Qpad + q] = q0acc;
+  aux[(int64_t)(TRAIN_NSEG + seg) * Qpad + q] = ldacc;
+  aux[(int64_t)(2 * TRAIN_NSEG + seg) * Qpad + q] = cnt;
+}
+
+// One warp per training quasar: Cholesky of the bordered matrix (as chol_generic_kernel), then
+// P = B^-1 column by column (lane c: forward + backward substitution for e_c, all lanes in lockstep so
+// every read of L is a broadcast), beta = P v, and the quasar's negative log likelihood
+// (spectrum_loss.m:40-52).  Gbuf row layout: [0,T) vech(B - I), [voff, voff + k) v.
+constexpr int TRC_WARPS = 4;
+__global__ void __launch_bounds__(TRC_WARPS * 32)
+train_chol_kernel(int64_t Q, int64_t Qpad, const double* __restrict__ Gbuf, const double* __restrict__ aux, int k,
+                  int ncol, int voff, double* __restrict__ fq, double* __restrict__ beta /* [Q][k] */,
+                  double* __restrict__ Pvech /* [Q][T] */) {
+  extern __shared__ double trc_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ld = k + 2, kb = k + 1, T = (k * (k + 1)) >> 1;
+  double* A = trc_smem + (size_t)warp * (kb * ld + k * kb + k);
+  double* Z = A + kb * ld;        // [k columns][k + 1]
+  double* invd = Z + k * kb;      // 1 / L_ii
+  const int64_t q = (int64_t)blockIdx.x * TRC_WARPS + warp;
+  if (q >= Q) return;
+  const double* row = Gbuf + q * ncol;
+  double q0v = 0.0, ldv = 0.0, cnt = 0.0;
+  for (int g = 0; g < TRAIN_NSEG; ++g) {
+    q0v += aux[(int64_t)g * Qpad + q];
+    ldv += aux[(int64_t)(TRAIN_NSEG + g) * Qpad + q];
+    cnt += aux[(int64_t)(2 * TRAIN_NSEG + g) * Qpad + q];
+  }
+  for (int i = 0; i < k; ++i)
+    for (int l = lane; l <= i; l += 32) A[i * ld + l] = row[((i * (i + 1)) >> 1) + l] + (l == i ? 1.0 : 0.0);
+  for (int l = lane; l < k; l += 32) A[k * ld + l] = row[voff + l];
+  if (lane == 0) A[k * ld + k] = q0v;
+  __syncwarp();
+  double pprod = 1.0;
+  int esum = 0;
+  for (int j = 0; j < k; ++j) {
+    const double piv = A[j * ld + j];
+    const double inv = rsqrt(piv);
+    {
+      pprod *= piv;
+      const int hi = __double2hiint(pprod);
+      const int e = ((hi >> 20) & 0x7ff) - 1023;
+      if (piv > 0.0 && e > -1000 && e < 1000) {
+        esum += e;
+        pprod = __hiloint2double(hi - (e << 20), __double2loint(pprod));
+      }
+    }
+    __syncwarp();
+    for (int i = j + lane; i <= k; i += 32) A[i * ld + j] *= inv;   // includes the diagonal: L_jj = sqrt(piv)
+    __syncwarp();
+    for (int l = j + 1; l <= k; ++l) {
+      const double Llj = A[l * ld + j];
+      for (int i = l + lane; i <= k; i += 32) A[i * ld + l] = fma(-A[i * ld + j], Llj, A[i * ld + l]);
+    }
+    __syncwarp();
+  }
+  for (int i = lane; i < k; i += 32) invd[i] = 1.0 / A[i * ld + i];
+  __syncwarp();
+  for (int c0 = 0; c0 < k; c0 += 32) {
+    const int c = c0 + lane;
+    const bool act = c < k;
+    double* z = Z + (size_t)(act ? c : 0) * kb;
+    if (act) {
+      for (int i = 0; i < k; ++i) {           // L z = e_c
+        double t = (i == c) ? 1.0 : 0.0;
+        for (int j = 0; j < i; ++j) t = fma(-A[i * ld + j], z[j], t);
+        z[i] = t * invd[i];
+      }
+      for (int i = k - 1; i >= 0; --i) {      // L' x = z  (in place)
+        double t = z[i];
+        for (int j = i + 1; j < k; ++j) t = fma(-A[j * ld + i], z[j], t);
+        z[i] = t * invd[i];
+      }
+      double b = 0.0;                          // beta_c = sum_l P_cl v_l,  v = L t  with t in the border row
+      for (int l = 0; l < k; ++l) b = fma(z[l], row[voff + l], b);
+      beta[q * k + c] = b;
+      double* Pq = Pvech + q * T;
+      for (int i = c; i < k; ++i) Pq[((i * (i + 1)) >> 1) + c] = z[i];
+    }
+  }
+  if (lane == 0) {
+    const double qq = A[k * ld + k];           // q0 - t't = y' K^-1 y
+    const double logdet = fma((double)esum, 0.693147180559945309417232, log(pprod));
+    fq[q] = 0.5 * (qq + (ldv + logdet) + cnt * LOG_2PI);   // spectrum_loss.m:48-52
+  }
+}
+
+// Gradient accumulation: one warp per rest-frame pixel p, looping over a slice of the training
+// quasars.  Lane c holds vech columns c, c + 32, ...: Phi2_p[c] = (2 - delta) M_pa M_pb for the
+// quadratic form M_p P_q M_p', and the running sums S_p = sum_q P_q / d_qp.  Lane j < k holds M_pj
+// and the running sum_q alpha_qp beta_qj.
+constexpr int TRG_WARPS = 8;
+__global__ void __launch_bounds__(TRG_WARPS * 32)
+train_grad_kernel(int64_t Q, int n, int k, const double* __restrict__ Mx /* x: vec M, column-major n x k */,
+                  const double* __restrict__ E, const double* __restrict__ beta, const double* __restrict__ Pvech,
+                  TrainConsts tc, int nsplit, double* __restrict__ A1part /* [nsplit][n][k] */,
+                  double* __restrict__ Spart /* [nsplit][n][T] */, double* __restrict__ gpart /* [nsplit][n][4] */) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = blockIdx.x * TRG_WARPS + warp;
+  if (p >= n) return;
+  const int split = blockIdx.y;
+  const int T = (k * (k + 1)) >> 1;
+  const int64_t qa = (Q * split) / nsplit, qb = (Q * (split + 1)) / nsplit;
+  double phi2[TRAIN_NC], S[TRAIN_NC];
+#pragma unroll
+  for (int i = 0; i < TRAIN_NC; ++i) {
+    const int c = lane + 32 * i;
+    double v = 0.0;
+    if (c < T) {
+      int a = (int)((sqrt(8.0 * c + 1.0) - 1.0) * 0.5);
+      while (a * (a + 1) / 2 > c) --a;
+      while ((a + 1) * (a + 2) / 2 <= c) ++a;
+      const int b = c - a * (a + 1) / 2;
+      v = Mx[(int64_t)a * n + p] * Mx[(int64_t)b * n + p] * (a == b ? 1.0 : 2.0);
+    }
+    phi2[i] = v;
+    S[i] = 0.0;
+  }
+  const double Mpj = lane < k ? Mx[(int64_t)lane * n + p] : 0.0;
+  double A1 = 0.0, g_om = 0.0, g_c0 = 0.0, g_tau = 0.0, g_beta = 0.0;
+  const int64_t QN = Q * n;
+  for (int64_t q = qa; q < qb; ++q) {
+    const int64_t e = q * n + p;
+    const double dinv = E[e];
+    if (dinv == 0.0) continue;              // missing pixel of this quasar (warp-uniform)
+    const double* Pq = Pvech + q * T;
+    double Pv[TRAIN_NC];
+    double h = 0.0;
+#pragma unroll
+    for (int i = 0; i < TRAIN_NC; ++i) {
+      const int c = lane + 32 * i;
+      Pv[i] = c < T ? Pq[c] : 0.0;
+      h = fma(phi2[i], Pv[i], h);
+    }
+    const double bj = lane < k ? beta[q * k + lane] : 0.0;
+    double mb = Mpj * bj;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      h += __shfl_xor_sync(0xffffffffu, h, o);
+      mb += __shfl_xor_sync(0xffffffffu, mb, o);
+    }
+    const double y0 = E[QN + e], osf = E[2 * QN + e], sf = E[3 * QN + e], odab = E[4 * QN + e], ll = E[5 * QN + e];
+    const double alpha = dinv * (y0 - mb);                    // spectrum_loss.m:46
+    const double dk = dinv - dinv * dinv * h;                 // :59
+    const double t = alpha * alpha - dk;
+    g_om = fma(osf * sf, t, g_om);                            // :62
+    g_c0 = fma(tc.c_0 * osf, t, g_c0);                        // :65-66
+    const double da2 = osf * odab;
+    g_tau = fma(da2, t, g_tau);                               // :69-70
+    g_beta = fma(da2 * ll, t, g_beta);                        // :73-74
+    A1 = fma(alpha, bj, A1);                                  // :56 first term (M' alpha = beta)
+#pragma unroll
+    for (int i = 0; i < TRAIN_NC; ++i) S[i] = fma(dinv, Pv[i], S[i]);   // :55-56 second term
+  }
+  const int64_t o = (int64_t)split * n + p;
+  if (lane < k) A1part[o * k + lane] = A1;
+#pragma unroll
+  for (int i = 0; i < TRAIN_NC; ++i) {
+    const int c = lane + 32 * i;
+    if (c < T) Spart[o * T + c] = S[i];
+  }
+  if (lane == 0) {
+    gpart[o * 4 + 0] = g_om; gpart[o * 4 + 1] = g_c0; gpart[o * 4 + 2] = g_tau; gpart[o * 4 + 3] = g_beta;
+  }
+}
+
+// g = [vec dM; dlog_omega] from the per-split partial sums (added in a fixed order), and the three
+// per-pixel scalar partials gsc[p][3] that the host adds up (objective.m:50-56, :73).
+__global__ void train_finish_kernel(int n, int k, int nsplit, const double* __restrict__ Mx,
+                                    const double* __restrict__ A1part, const double* __restrict__ Spart,
+                                    const double* __restrict__ gpart, double* __restrict__ g,
+                                    double* __restrict__ gsc) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int T = (k * (k + 1)) >> 1;
+  if (idx >= n * (k + 1)) return;
+  const int p = idx % n, j = idx / n;
+  if (j < k) {
+    double a1 = 0.0, ms = 0.0;
+    for (int s = 0; s < nsplit; ++s) a1 += A1part[((int64_t)s * n + p) * k + j];
+    for (int l = 0; l < k; ++l) {
+      const int hi = l > j ? l : j, lo = l > j ? j : l;
+      const int c = ((hi * (hi + 1)) >> 1) + lo;
+      double sp = 0.0;
+      for (int s = 0; s < nsplit; ++s) sp += Spart[((int64_t)s * n + p) * T + c];
+      ms = fma(Mx[(int64_t)l * n + p], sp, ms);
+    }
+    g[(int64_t)j * n + p] = -a1 + ms;                         // spectrum_loss.m:56
+  } else {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    for (int s = 0; s < nsplit; ++s) {
+      const double* gp = gpart + ((int64_t)s * n + p) * 4;
+      s0 += gp[0]; s1 += gp[1]; s2 += gp[2]; s3 += gp[3];
+    }
+    g[(int64_t)k * n + p] = -s0;                              // :62
+    gsc[p * 3 + 0] = -s1; gsc[p * 3 + 1] = -s2; gsc[p * 3 + 2] = -s3;
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
 // K3: per quasar log-mean-exp over samples, first-index argmax, posteriors.
 // process_qsos.m:202-212, :223-229; generate_ascii_catalog.m:73 (nanmax, first maximum wins).
 // ----------------------------------------------------------------------------------------------

@@ -162,6 +162,21 @@ int dla_eval_spectra(dla_ctx *ctx, int64_t Q, const int64_t *spec_ptr, const dou
                      double *model_posteriors, int32_t *map_index,
                      double *min_z_dla, double *max_z_dla);
 
+/* ---- training objective -------------------------------------------------
+ * objective.m:12-75 over spectrum_loss.m:14-76: f(x) = -sum_i log N(y_i; 0, M M' + diag(d_i)) and
+ * its gradient, x = [vec M (num_pixels x k, column-major); log_omega (num_pixels); log c_0;
+ * log tau_0; log beta], k = the context's rank (<= 32 here).  The training set stays resident on
+ * the device between calls (an L-BFGS run evaluates the objective many times):
+ *   centered_rest_fluxes, lya_1pzs, rest_noise_variances  [num_quasars][num_pixels], ROW-major
+ *   (one spectrum contiguous; MATLAB's arrays are the transpose), NaN in the flux = missing pixel
+ *   (objective.m:42).  apply_priors != 0 adds the tau_0 / beta priors of objective.m:60-71.
+ * A multi-GPU run gives every rank its own slice of the quasars and SUMS f and g over ranks (the
+ * one all-reduce of the pipeline; priors added once) -- see gp_dla_detection_b200/learn_qso_model.py. */
+int dla_train_set_data(dla_ctx *ctx, int64_t num_quasars, int64_t num_pixels,
+                       const double *centered_rest_fluxes, const double *lya_1pzs,
+                       const double *rest_noise_variances);
+int dla_train_objective(dla_ctx *ctx, const double *x, int32_t apply_priors, double *f, double *g);
+
 int dla_get_timing(const dla_ctx *ctx, dla_timing *out);
 
 /* Unit seams (one call = one reference call; for parity tests and for running

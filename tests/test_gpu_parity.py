@@ -198,3 +198,37 @@ def test_device_side_preparation_matches_host_preparation(oracle, cfg, mask_gath
     assert_parity(b, ref)
     rel = np.abs(a["sample_log_likelihoods_dla"] - b["sample_log_likelihoods_dla"]) / np.abs(a["sample_log_likelihoods_dla"])
     print(cfg, mask_gather, "device prep vs host prep, worst rel", rel.max())
+
+
+@pytest.mark.parametrize("Q,n,k", [(5, 90, 5), (37, 1217, 20), (130, 333, 12)])
+def test_training_objective_matches_the_objective_m_restatement(Q, n, k):
+    """dla_train_objective (objective.m / spectrum_loss.m on the GPU: DMMA contraction over training quasars,
+    per-quasar Cholesky + inverse, per-pixel gradient accumulation) against the numpy restatement."""
+    from gp_dla_detection_b200.learn_qso_model import TrainingObjective
+    from oracle import train_oracle as T
+    x, y, l1, nv = T.make_training_set(Q, k=k, n_rest=n, seed=7 + Q)
+    f_ref, g_ref = T.objective(x, y, l1, nv, apply_priors=True)
+    obj = TrainingObjective(y, l1, nv, k)
+    try:
+        f, g = obj(x)
+        f2, g2 = obj(x)
+    finally:
+        obj.close()
+    assert abs(f - f_ref) <= 1e-10 * abs(f_ref)
+    scale = np.max(np.abs(g_ref))
+    assert np.max(np.abs(g - g_ref)) <= 1e-9 * scale, np.max(np.abs(g - g_ref)) / scale
+    assert np.max(np.abs(g[-3:] - g_ref[-3:]) / np.abs(g_ref[-3:])) <= 1e-8
+    assert f == f2 and np.array_equal(g, g2)          # fixed summation order: bitwise reproducible
+    print("training objective: f rel err", abs(f - f_ref) / abs(f_ref), "g err/scale", np.max(np.abs(g - g_ref)) / scale)
+
+
+def test_learn_qso_model_decreases_the_objective():
+    from gp_dla_detection_b200.learn_qso_model import TrainingObjective, learn_qso_model
+    from oracle import train_oracle as T
+    x, y, l1, nv = T.make_training_set(64, k=4, n_rest=120, seed=3)
+    obj = TrainingObjective(y, l1, nv, 4)
+    f0 = obj(x)[0]
+    obj.close()
+    rest = 911.75 + 0.25 * np.arange(120)
+    model, f1, res = learn_qso_model(rest, np.zeros(120), y, l1, nv, k=4, max_iter=30, x0=x)
+    assert f1 < f0 and model.M.shape == (120, 4) and np.isfinite(model.log_beta)
