@@ -159,11 +159,21 @@ struct ColGeom {
 static ColGeom col_geom(int k) {
   if (k <= dla::KMAX) return {false, dla::NCOL, dla::VOFF, 1, dla::NT / 2};
   const int T8 = (int)round_up((int64_t)k * (k + 1) / 2, 8);
-  const int ncol = T8 + (int)round_up(k, 8);
-  const int ntile = ncol / 8;
+  const int ntile = (T8 + (int)round_up(k, 8)) / 8;
   const int nblocks = (ntile + dla::NT - 1) / dla::NT;
-  const int tpw = (ntile + 2 * nblocks - 1) / (2 * nblocks);
-  return {true, ncol, T8, nblocks, tpw};
+  const int tpw = std::max(8, (ntile + 2 * nblocks - 1) / (2 * nblocks));
+  return {true, nblocks * 2 * tpw * 8 /* zero columns pad the last block */, T8, nblocks, tpw};
+}
+
+// contract_block_kernel<TPW> for the runtime tiles-per-warp of a column geometry
+template <typename... Args>
+static void launch_contract_block(int tpw, dim3 grid, size_t smem, cudaStream_t st, Args... args) {
+  switch (tpw) {
+#define CB_CASE(T) case T: dla::contract_block_kernel<T><<<grid, dla::K2_THREADS, smem, st>>>(args...); break;
+    CB_CASE(8) CB_CASE(9) CB_CASE(10) CB_CASE(11) CB_CASE(12) CB_CASE(13) CB_CASE(14) CB_CASE(15)
+#undef CB_CASE
+    default: break;
+  }
 }
 
 static int k1_warps_for(int raw_stride) {
@@ -218,10 +228,10 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   if (gen.generic) {
     const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
     dim3 grid((unsigned)((int64_t)ch.nq * nsb), (unsigned)gen.nblocks);
-    dla::contract_block_kernel<<<grid, dla::K2_THREADS, smem, st>>>(in.desc, ch.q0, nsb, W, U, B, c->d_G.as<double>(),
-                                                                     gen.ncol, gen.voff / 8, gen.tpw);
+    launch_contract_block(gen.tpw, grid, smem, st, in.desc, ch.q0, nsb, (const double*)W, (const double*)U,
+                          (const double*)B, c->d_G.as<double>(), gen.ncol, gen.voff / 8);
     dim3 g2((unsigned)((S + 1 + dla::CHG_WARPS - 1) / dla::CHG_WARPS), (unsigned)ch.nq);
-    const size_t sm2 = (size_t)dla::CHG_WARPS * (k + 1) * (k + 2) * 8;
+    const size_t sm2 = dla::chg_smem_bytes(k);
     dla::chol_generic_kernel<<<g2, dla::CHG_WARPS * 32, sm2, st>>>(in.desc, ch.q0, nsb, S, c->d_G.as<double>(), aux,
                                                                     d_perm, sample_ll_chunk, ll_no, k, gen.ncol, gen.voff, nseg);
   } else if (!c->force_tile_k2) {
@@ -428,13 +438,16 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)dla::K2P_SMEM_BYTES));
-  CREATE_TRY(cudaFuncSetAttribute(dla::contract_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+#define CB_ATTR(T)                                                                                         \
+  CREATE_TRY(cudaFuncSetAttribute(dla::contract_block_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
+  CB_ATTR(8) CB_ATTR(9) CB_ATTR(10) CB_ATTR(11) CB_ATTR(12) CB_ATTR(13) CB_ATTR(14) CB_ATTR(15)
+#undef CB_ATTR
   CREATE_TRY(cudaFuncSetAttribute(dla::train_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   dla::TRC_WARPS * ((dla::TRAIN_KMAX + 1) * (dla::TRAIN_KMAX + 2) +
                                                     dla::TRAIN_KMAX * (dla::TRAIN_KMAX + 1) + dla::TRAIN_KMAX) * 8));
   CREATE_TRY(cudaFuncSetAttribute(dla::chol_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  dla::CHG_WARPS * (dla::KGEN_MAX + 1) * (dla::KGEN_MAX + 2) * 8));
+                                  (int)dla::chg_smem_bytes(dla::KGEN_MAX)));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #undef CREATE_TRY
@@ -503,7 +516,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
                       const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
                       const double* mu, const double* omega2, const double* noise_variance, const double* M,
                       const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
-                      const double* log_prior_no_dla) {
+                      const double* log_prior_no_dla, int max_pipe_chunks) {
   c->staged = false;
   c->ran = false;
   if (Q < 0 || Q > (int64_t)INT32_MAX) BAD_ARG(c, "dla_stage_batch: Q out of range");
@@ -548,7 +561,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
     const long double gq = col_geom(c->p.k).generic ? 8.0L * S_pad * col_geom(c->p.k).ncol : 0.0L;  // G rows
     for (int64_t q = 0; q < Q; ++q) total += 16.0L * S_pad * c->h_desc[(size_t)q].npad + gq;
     const int64_t budget = c->p.workspace_bytes;
-    const int64_t pipe = std::min<int64_t>(4, Q / 8);
+    const int64_t pipe = std::min<int64_t>(max_pipe_chunks, Q / 8);
     const int64_t nch = std::max<int64_t>(std::max<int64_t>(1, pipe), (int64_t)ceill(total / budget));
     const long double target = total / nch;
     int64_t q = 0;
@@ -678,8 +691,9 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
                     const double* log_prior_no_dla) {
   if (!c) return DLA_ERR_BAD_ARG;
   c->dev_prep = false;
+  // everything is resident before the first kernel: no reason to split beyond the workspace budget
   int rc = plan_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M,
-                      min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
+                      min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla, 1);
   if (rc != DLA_OK) return rc;
   CU_TRY(c, cudaEventRecord(c->ev[5], c->s_in));
   for (size_t i = 0; i < c->chunks.size(); ++i)
@@ -809,7 +823,7 @@ int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t*
   if (sample_ll && !c->p.store_sample_ll) BAD_ARG(c, "dla_eval_batch: sample_ll requested but store_sample_ll = 0");
   c->dev_prep = false;
   int rc = plan_batch(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M,
-                      min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla);
+                      min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla, 4);
   if (rc != DLA_OK) return rc;
   return run_pipelined(c, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
 }
@@ -917,7 +931,7 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
   // mu / omega2 / M are produced on the device: any non-NULL pointer satisfies the planner
   const double* dummy = fk;
   int rc = plan_batch(c, Q, pix_ptr.data(), pad_ptr.data(), padded, pidx, fk, dummy, dummy, nk,
-                      dummy, minz.data(), maxz.data(), log_prior_dla, log_prior_no_dla);
+                      dummy, minz.data(), maxz.data(), log_prior_dla, log_prior_no_dla, 4);
   if (rc == DLA_OK) {
     c->hin.lamk = lamk;
     c->hin.zq = z_qso;
@@ -1016,9 +1030,9 @@ int dla_train_objective(dla_ctx* c, const double* x, int32_t apply_priors, doubl
   {
     const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
     dim3 grid((unsigned)nqb, (unsigned)gen.nblocks);
-    dla::contract_block_kernel<<<grid, dla::K2_THREADS, smem, st>>>(
-        c->t_desc.as<QuasarDesc>(), 0, nqb, c->d_W.as<double>(), c->d_U.as<double>(), c->d_bmat.as<double>(),
-        c->d_G.as<double>(), gen.ncol, gen.voff / 8, gen.tpw);
+    launch_contract_block(gen.tpw, grid, smem, st, (const QuasarDesc*)c->t_desc.as<QuasarDesc>(), 0, nqb,
+                          (const double*)c->d_W.as<double>(), (const double*)c->d_U.as<double>(),
+                          (const double*)c->d_bmat.as<double>(), c->d_G.as<double>(), gen.ncol, gen.voff / 8);
   }
   {
     const size_t smem = (size_t)dla::TRC_WARPS * ((k + 1) * (k + 2) + k * (k + 1) + k) * 8;

@@ -1173,11 +1173,14 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
 // ----------------------------------------------------------------------------------------------
 constexpr int KGEN_MAX = 64;
 
+// TPW = eight-column tiles per warp (a column block = 2 TPW tiles).  The column count is padded with
+// zero columns to a whole number of blocks, so there is no per-tile predicate in the main loop; blocks
+// that hold only Phi columns (all but the last one or two) never touch U.
+template <int TPW>
 __global__ void __launch_bounds__(K2_THREADS, 1)
 contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, const double* __restrict__ Wbuf,
                       const double* __restrict__ Ubuf, const double* __restrict__ bmat,
-                      double* __restrict__ Gbuf /* [nq][S_pad][ncol] */, int ncol, int vtile /* first U tile */,
-                      int tpw /* active tiles per warp, <= 15 */) {
+                      double* __restrict__ Gbuf /* [nq][S_pad][ncol] */, int ncol, int vtile /* first U tile */) {
   extern __shared__ __align__(128) unsigned char k2_smem_raw[];
   double* smem = reinterpret_cast<double*>(k2_smem_raw);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)K2_STAGES * STAGE_DOUBLES);
@@ -1186,9 +1189,9 @@ contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, cons
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int npc = d.npad >> 2;
   const int nchunks = d.npad / KC;
-  const int ntile_total = ncol >> 3;
-  const int tile0 = cb * 2 * tpw;                       // first tile of this column block
-  const int ntb = min(2 * tpw, ntile_total - tile0);    // tiles in this block
+  constexpr int NTB = 2 * TPW;                          // tiles in a column block
+  const int tile0 = cb * NTB;                           // first tile of this column block
+  const bool has_v = tile0 + NTB > vtile;               // block-uniform
   const double* Wsrc = Wbuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
   const double* Usrc = Ubuf + d.wu_off + (int64_t)sb * npc * (TS * 4);
   const double* Bsrc = bmat + d.bmat_off / NCOL * ncol + (int64_t)tile0 * 32;
@@ -1198,13 +1201,13 @@ contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, cons
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  const uint32_t bbytes = (uint32_t)ntb * 32 * 8;  // one pixel quad of this block's B columns
+  constexpr uint32_t bbytes = (uint32_t)NTB * 32 * 8;  // one pixel quad of this block's B columns
   auto issue = [&](int c) {
     const int st = c % K2_STAGES;
     double* dst = smem + (size_t)st * STAGE_DOUBLES;
-    mbar_expect_tx(&full[st], 2 * STAGE_W_DOUBLES * 8 + (KC / 4) * bbytes);
+    mbar_expect_tx(&full[st], (has_v ? 2 : 1) * STAGE_W_DOUBLES * 8 + (KC / 4) * bbytes);
     bulk_g2s(dst, Wsrc + (int64_t)c * STAGE_W_DOUBLES, STAGE_W_DOUBLES * 8, &full[st]);
-    bulk_g2s(dst + STAGE_W_DOUBLES, Usrc + (int64_t)c * STAGE_W_DOUBLES, STAGE_W_DOUBLES * 8, &full[st]);
+    if (has_v) bulk_g2s(dst + STAGE_W_DOUBLES, Usrc + (int64_t)c * STAGE_W_DOUBLES, STAGE_W_DOUBLES * 8, &full[st]);
 #pragma unroll
     for (int kc = 0; kc < KC / 4; ++kc)
       bulk_g2s(dst + 2 * STAGE_W_DOUBLES + kc * (NCOL * 4), Bsrc + ((int64_t)c * (KC / 4) + kc) * ncol * 4, bbytes,
@@ -1215,12 +1218,12 @@ contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, cons
     for (int c = 0; c < pre; ++c) issue(c);
   }
   const int mrow = warp & 3, half = warp >> 2;
-  constexpr int TPW = NT / 2;
   double acc[TPW][4];
 #pragma unroll
   for (int j = 0; j < TPW; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0;
-  const int wt0 = half * tpw;                 // this warp's first tile within the block
-  const int nact = max(0, min(tpw, ntb - wt0));
+  const int wt0 = half * TPW;                 // this warp's first tile within the block
+  // tiles [0, nw) of this warp take A = W, the rest A = U (warp-uniform; 0 <= nw <= TPW)
+  const int nw = min(TPW, max(0, vtile - (tile0 + wt0)));
 
   for (int c = 0; c < nchunks; ++c) {
     const int st = c % K2_STAGES;
@@ -1232,14 +1235,21 @@ contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, cons
     for (int kc = 0; kc < KC / 4; ++kc) {
       const double aw0 = Ws[kc * (TS * 4) + (2 * mrow) * 32 + lane];
       const double aw1 = Ws[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
-      const double au0 = Us[kc * (TS * 4) + (2 * mrow) * 32 + lane];
-      const double au1 = Us[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
       const double* bp = Bs + kc * (NCOL * 4) + wt0 * 32 + lane;
+      if (nw == TPW) {
 #pragma unroll
-      for (int j = 0; j < TPW; ++j) {
-        if (j < nact) {  // warp-uniform
+        for (int j = 0; j < TPW; ++j) {
           const double b = bp[j * 32];
-          const bool isv = (tile0 + wt0 + j) >= vtile;
+          dmma884(acc[j][0], acc[j][1], aw0, b);
+          dmma884(acc[j][2], acc[j][3], aw1, b);
+        }
+      } else {
+        const double au0 = Us[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+        const double au1 = Us[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+#pragma unroll
+        for (int j = 0; j < TPW; ++j) {
+          const double b = bp[j * 32];
+          const bool isv = j >= nw;
           dmma884(acc[j][0], acc[j][1], isv ? au0 : aw0, b);
           dmma884(acc[j][2], acc[j][3], isv ? au1 : aw1, b);
         }
@@ -1255,10 +1265,8 @@ contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, cons
     double* g0 = Gbuf + ((int64_t)ql * S_pad + (int64_t)sb * TS + r0) * ncol + (tile0 + wt0) * 8 + 2 * (lane & 3);
 #pragma unroll
     for (int j = 0; j < TPW; ++j) {
-      if (j < nact) {
-        *reinterpret_cast<double2*>(g0 + j * 8) = make_double2(acc[j][0], acc[j][1]);
-        *reinterpret_cast<double2*>(g0 + (int64_t)8 * ncol + j * 8) = make_double2(acc[j][2], acc[j][3]);
-      }
+      *reinterpret_cast<double2*>(g0 + j * 8) = make_double2(acc[j][0], acc[j][1]);
+      *reinterpret_cast<double2*>(g0 + (int64_t)8 * ncol + j * 8) = make_double2(acc[j][2], acc[j][3]);
     }
   }
 }
@@ -1267,14 +1275,31 @@ contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, cons
 // right-looking Cholesky over the first k columns; the corner ends as q0 - t^T t and the product of
 // the pivots (kept in [1,2) with an integer exponent) gives log|B| (log_mvnpdf_low_rank.m:23-32).
 constexpr int CHG_WARPS = 4;
+// shared-memory bytes of chol_generic_kernel: the trailing-update index table + one matrix per warp
+__host__ __device__ constexpr size_t chg_smem_bytes(int k) {
+  return (size_t)(((k + 1) * (k + 2) / 2 + 1) / 2 * 2) * 4 + (size_t)CHG_WARPS * (k + 1) * (k + 2) * 8;
+}
 __global__ void __launch_bounds__(CHG_WARPS * 32)
 chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S, const double* __restrict__ Gbuf,
                     const double* __restrict__ aux, const int32_t* __restrict__ perm, double* __restrict__ sample_ll,
                     double* __restrict__ ll_no_dla, int k, int ncol, int voff, int nseg) {
-  extern __shared__ double chg_smem[];
+  extern __shared__ __align__(16) unsigned char chg_smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ld = k + 2, kb = k + 1;
-  double* A = chg_smem + (size_t)warp * kb * ld;
+  // tab[e] = (i << 16) | l for the elements (i >= l) of the lower triangle ordered by DESCENDING column l:
+  // the trailing update of elimination step j touches exactly the first (k-j)(k-j+1)/2 entries, so the 32
+  // lanes walk a dense list instead of one short column at a time
+  const int ntab = (kb * (kb + 1)) >> 1;
+  uint32_t* tab = reinterpret_cast<uint32_t*>(chg_smem_raw);
+  double* A = reinterpret_cast<double*>(chg_smem_raw + (size_t)((ntab + 1) / 2 * 2) * 4) + (size_t)warp * kb * ld;
+  for (int e = threadIdx.x; e < ntab; e += blockDim.x) {
+    int a = (int)((sqrtf(8.0f * e + 1.0f) - 1.0f) * 0.5f);
+    while (a * (a + 1) / 2 > e) --a;
+    while ((a + 1) * (a + 2) / 2 <= e) ++a;
+    const int l = k - a, i = l + (e - a * (a + 1) / 2);
+    tab[e] = ((uint32_t)i << 16) | (uint32_t)l;
+  }
+  __syncthreads();
   const int64_t S_pad = (int64_t)nsb * TS;
   const int ql = blockIdx.y;
   const int64_t s = (int64_t)blockIdx.x * CHG_WARPS + warp;
@@ -1303,9 +1328,12 @@ chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_
     }
     for (int i = j + 1 + lane; i <= k; i += 32) A[i * ld + j] *= inv;
     __syncwarp();
-    for (int l = j + 1; l <= k; ++l) {
-      const double Llj = A[l * ld + j];
-      for (int i = l + lane; i <= k; i += 32) A[i * ld + l] = fma(-A[i * ld + j], Llj, A[i * ld + l]);
+    const int m = k - j, cnt = (m * (m + 1)) >> 1;
+    const double* colj = A + j;
+    for (int e = lane; e < cnt; e += 32) {
+      const uint32_t t = tab[e];
+      const int i = (int)(t >> 16), l = (int)(t & 0xffffu);
+      A[i * ld + l] = fma(-colj[i * ld], colj[l * ld], A[i * ld + l]);
     }
     __syncwarp();
   }
