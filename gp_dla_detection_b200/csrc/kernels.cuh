@@ -1307,10 +1307,15 @@ chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_
   const double* row = Gbuf + ((int64_t)ql * S_pad + s) * ncol;
   double q0v, ldv;
   aux_sums(aux, ql, nseg, S_pad, s, q0v, ldv);
-  for (int i = 0; i < k; ++i)
-    for (int l = lane; l <= i; l += 32) A[i * ld + l] = row[((i * (i + 1)) >> 1) + l] + (l == i ? 1.0 : 0.0);
-  for (int l = lane; l < k; l += 32) A[k * ld + l] = row[voff + l];
-  if (lane == 0) A[k * ld + k] = q0v;
+  // bordered matrix from the G row: every table entry is one element of the lower triangle
+  for (int e = lane; e < ntab; e += 32) {
+    const uint32_t t = tab[e];
+    const int i = (int)(t >> 16), l = (int)(t & 0xffffu);
+    double v;
+    if (i < k) v = row[((i * (i + 1)) >> 1) + l] + (l == i ? 1.0 : 0.0);
+    else v = (l < k) ? row[voff + l] : q0v;
+    A[i * ld + l] = v;
+  }
   __syncwarp();
   double pprod = 1.0;
   int esum = 0;
@@ -1330,7 +1335,26 @@ chol_generic_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_
     __syncwarp();
     const int m = k - j, cnt = (m * (m + 1)) >> 1;
     const double* colj = A + j;
-    for (int e = lane; e < cnt; e += 32) {
+    int e = lane;
+    for (; e + 96 < cnt; e += 128) {  // four independent elements in flight per lane
+      uint32_t t[4];
+      double a[4], x[4], y[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) t[u] = tab[e + 32 * u];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = (int)(t[u] >> 16), l = (int)(t[u] & 0xffffu);
+        x[u] = colj[i * ld];
+        y[u] = colj[l * ld];
+        a[u] = A[i * ld + l];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = (int)(t[u] >> 16), l = (int)(t[u] & 0xffffu);
+        A[i * ld + l] = fma(-x[u], y[u], a[u]);
+      }
+    }
+    for (; e < cnt; e += 32) {
       const uint32_t t = tab[e];
       const int i = (int)(t >> 16), l = (int)(t & 0xffffu);
       A[i * ld + l] = fma(-colj[i * ld], colj[l * ld], A[i * ld + l]);
