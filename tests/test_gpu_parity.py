@@ -232,3 +232,69 @@ def test_learn_qso_model_decreases_the_objective():
     rest = 911.75 + 0.25 * np.arange(120)
     model, f1, res = learn_qso_model(rest, np.zeros(120), y, l1, nv, k=4, max_iter=30, x0=x)
     assert f1 < f0 and model.M.shape == (120, 4) and np.isfinite(model.log_beta)
+
+
+def test_degenerate_shapes_do_not_crash(oracle):
+    """Q = 0, S = 0 (only the no-DLA likelihood), S = 1, very short spectra (n < 16), NaN flux in one quasar."""
+    params, model, samples, sp, prepared = prepared_config("tiny", 3, 8)
+    k = prepared[0].M.shape[1]
+    # Q = 0
+    with DlaContext(k=k, num_samples=8) as ctx:
+        ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+        out = ctx.eval_batch(PackedBatch([], k), np.zeros(0), np.zeros(0))
+        assert out["log_likelihoods_dla"].shape == (0,)
+    # S = 0: no hypotheses; the no-DLA likelihood is still evaluated
+    with DlaContext(k=k, num_samples=0) as ctx:
+        ctx.set_samples(np.zeros(0), np.zeros(0))
+        out = ctx.eval_batch(PackedBatch(prepared, k), sp.log_priors_dla, sp.log_priors_no_dla)
+    for q, p in enumerate(prepared):
+        ref = oracle.log_mvnpdf_low_rank_c(p.flux, p.mu, p.M, p.omega2 + p.noise_variance)
+        assert abs(out["log_likelihoods_no_dla"][q] - ref) <= 1e-10 * abs(ref)
+    # S = 1 and a quasar cut down to 9 kept pixels
+    import copy
+    short = copy.deepcopy(prepared[0])
+    short.n = 9
+    for name in ("flux", "mu", "omega2", "noise_variance"):
+        setattr(short, name, getattr(short, name)[:9].copy())
+    short.M = np.asfortranarray(short.M[:9])
+    short.profile_index = short.profile_index[:9].copy()
+    off, nhi = samples.offset_samples[:1].copy(), samples.nhi_samples[:1].copy()
+    with DlaContext(k=k, num_samples=1) as ctx:
+        ctx.set_samples(off, nhi)
+        got = ctx.eval_batch(PackedBatch([short, prepared[1]], k), sp.log_priors_dla[:2], sp.log_priors_no_dla[:2])
+
+    class S1:
+        offset_samples, nhi_samples = off, nhi
+    ref = oracle_batch(oracle, [short, prepared[1]], S1, sp.log_priors_dla[:2], sp.log_priors_no_dla[:2])
+    assert_parity(got, ref, check_map=False)
+    assert list(got["map_ind"]) == [0, 0]
+    # NaN flux: that quasar's likelihoods are NaN (as in MATLAB), the others are untouched
+    bad = copy.deepcopy(prepared)
+    bad[1].flux = bad[1].flux.copy()
+    bad[1].flux[5] = np.nan
+    a = _run_gpu(prepared, samples, k, 8, sp.log_priors_dla, sp.log_priors_no_dla)
+    b = _run_gpu(bad, samples, k, 8, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert np.all(np.isnan(b["sample_log_likelihoods_dla"][1])) and np.isnan(b["log_likelihoods_no_dla"][1])
+    assert b["map_ind"][1] == -1
+    for q in (0, 2):
+        assert np.array_equal(a["sample_log_likelihoods_dla"][q], b["sample_log_likelihoods_dla"][q])
+
+
+def test_config4_dense_sampling_properties():
+    """BASELINE config 4 shape (num_dla_samples = 100000) on two quasars: size-independent properties, and the
+    first 10000 hypotheses of the dense set agree with a run on those 10000 alone (position in the sorted
+    set only changes which series length a hypothesis shares with its warp)."""
+    params, model, samples, sp, prepared = prepared_config("config4", 2, 100000)
+    S = 100000
+    got = _run_gpu(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    ll = got["sample_log_likelihoods_dla"]
+    assert ll.shape == (2, S) and np.all(np.isfinite(ll))
+    norm = np.exp(ll - (got["log_likelihoods_dla"][:, None] + np.log(S))).sum(axis=1)     # K10
+    assert np.allclose(norm, 1.0, rtol=1e-10)
+    assert np.array_equal(got["map_ind"], np.argmax(ll, axis=1))
+
+    class Sub:
+        offset_samples, nhi_samples = samples.offset_samples[:10000], samples.nhi_samples[:10000]
+    sub = _run_gpu(prepared, Sub, 20, 10000, sp.log_priors_dla, sp.log_priors_no_dla)
+    rel = np.abs(sub["sample_log_likelihoods_dla"] - ll[:, :10000]) / np.abs(ll[:, :10000])
+    assert rel.max() <= 1e-10
