@@ -114,6 +114,7 @@ struct dla_ctx {
   bool have_samples = false;
   bool force_pixel_lane_k1 = false;  // DLA_B200_K1=pixel: always use voigt_weights_kernel
   bool force_tile_k2 = false;        // DLA_B200_K2=tile: one CTA per tile (contract_chol_kernel)
+  bool use_fused = false;            // DLA_B200_FUSED=1: fused_voigt_contract_kernel (W/U never leave the SM)
   int num_sms = 148;
   // staged batch
   int64_t Q = 0;
@@ -207,7 +208,10 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[1], st));
   int nseg = 1;  // partial (q0, log|D|) sums per sample that K1 leaves in aux
-  if (ch.all_ident && num_lines == 3 && !c->force_pixel_lane_k1) {
+  const bool fused = c->use_fused && ch.all_ident && num_lines == 3 && !gen.generic;
+  if (fused) {
+    // K1 runs inside the contraction kernel (producer warps)
+  } else if (ch.all_ident && num_lines == 3 && !c->force_pixel_lane_k1) {
     nseg = std::min(dla::K1S_NSEG_MAX, std::max(dla::K1S_NSEG_MIN, (ch.max_npad / 4 + 79) / 80));
     const int gmax = (ch.max_npad / 4 + nseg - 1) / nseg + 1;  // groups of 4 pixels per segment
     const int lam_cap = 4 * gmax + 8;
@@ -225,7 +229,13 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
         num_lines, raw_stride);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[2], st));
-  if (gen.generic) {
+  if (fused) {
+    const int64_t ntiles = (int64_t)ch.nq * nsb;
+    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
+    dla::fused_voigt_contract_kernel<<<grid, dla::KF_THREADS, dla::KF_SMEM_BYTES, st>>>(
+        in.desc, ch.q0, nsb, (int)ntiles, S, d_offset, d_nhi, in.padded, in.pix4, c->d_etab256.as<double>(), B, d_perm,
+        sample_ll_chunk, ll_no, k);
+  } else if (gen.generic) {
     const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
     dim3 grid((unsigned)((int64_t)ch.nq * nsb), (unsigned)gen.nblocks);
     launch_contract_block(gen.tpw, grid, smem, st, in.desc, ch.q0, nsb, (const double*)W, (const double*)U,
@@ -428,6 +438,8 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     for (int i = 0; i < 256; ++i) e256[i] = exp2(i / 256.0);
     CREATE_TRY(c->d_etab256.ensure(sizeof e256));
     CREATE_TRY(cudaMemcpy(c->d_etab256.p, e256, sizeof e256, cudaMemcpyHostToDevice));
+    const char* fu = getenv("DLA_B200_FUSED");
+    c->use_fused = fu && strcmp(fu, "1") == 0;
     const char* k2 = getenv("DLA_B200_K2");
     c->force_tile_k2 = k2 && strcmp(k2, "tile") == 0;
     c->num_sms = prop.multiProcessorCount;
@@ -436,6 +448,8 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
   }
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
+  CREATE_TRY(cudaFuncSetAttribute(dla::fused_voigt_contract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)dla::KF_SMEM_BYTES));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)dla::K2P_SMEM_BYTES));
 #define CB_ATTR(T)                                                                                         \

@@ -1163,6 +1163,200 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
 }
 
 // ----------------------------------------------------------------------------------------------
+// Fused K1 + K2 (opt-in, DLA_B200_FUSED=1): the persistent contraction with the Voigt/weights work
+// done by FOUR producer warps (one per SM sub-partition, so that their FP64 instructions spread evenly
+// over the four FP64 pipes they share with DMMA).  W and U never exist in HBM: a producer lane owns one
+// hypothesis of the tile; per K-chunk of 8 pixels, warp pair 0 produces pixels 0-3 and pair 1 pixels
+// 4-7.  The raw transmissions go through a 32-pixel shared-memory ring (phase 1 runs one chunk ahead of
+// phase 2; one 128-thread named barrier per chunk), the weights are written straight into the stage the
+// DMMA warps read, and B arrives by TMA.  full[stage]: 4 producer-warp arrivals + the TMA transaction;
+// empty[stage]: 8 DMMA-warp arrivals.  The per-hypothesis sums q0 / log|D| reach the epilogue through a
+// double-buffered shared array guarded by its own mbarrier.
+// ----------------------------------------------------------------------------------------------
+constexpr int KF_STAGES = 3;
+constexpr int KF_RING = 32;                                       // raw-transmission ring, pixels
+constexpr int KF_THREADS = 384;                                   // 8 DMMA warps + 4 producer warps
+constexpr int KF_STAGE_DOUBLES = K2P_STAGE_DOUBLES;               // W 512 | U 512 | B 1920
+constexpr size_t KF_SMEM_DOUBLES = (size_t)KF_STAGES * KF_STAGE_DOUBLES + K2P_C_DOUBLES + KF_RING * TS +
+                                   2 * 2 * TS * 2 + 256;
+constexpr size_t KF_SMEM_BYTES = KF_SMEM_DOUBLES * 8 + (2 * KF_STAGES + 2) * 8;
+
+__device__ __forceinline__ void producer_bar_sync() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
+
+__global__ void __launch_bounds__(KF_THREADS, 1)
+fused_voigt_contract_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int ntiles, int64_t S,
+                            const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
+                            const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
+                            const double* __restrict__ etab256, const double* __restrict__ bmat,
+                            const int32_t* __restrict__ perm, double* __restrict__ sample_ll,
+                            double* __restrict__ ll_no_dla, int k) {
+  extern __shared__ __align__(128) unsigned char k2_smem_raw[];
+  double* smem = reinterpret_cast<double*>(k2_smem_raw);
+  double* Cs = smem + (size_t)KF_STAGES * KF_STAGE_DOUBLES;
+  double* ring = Cs + K2P_C_DOUBLES;                 // [KF_RING][TS]
+  double* auxs = ring + KF_RING * TS;                // [tile parity 2][pair 2][TS][2]
+  double* etab_s = auxs + 2 * 2 * TS * 2;
+  uint64_t* full = reinterpret_cast<uint64_t*>(etab_s + 256);
+  uint64_t* empty = full + KF_STAGES;
+  uint64_t* auxbar = empty + KF_STAGES;              // [2]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int s = 0; s < KF_STAGES; ++s) {
+      mbar_init(&full[s], 5);                        // 4 producer warps + the expect_tx arrival
+      mbar_init(&empty[s], K2P_CONSUMER_WARPS);
+    }
+    mbar_init(&auxbar[0], 4);
+    mbar_init(&auxbar[1], 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (tid < 256) etab_s[tid] = etab256[tid];
+  __syncthreads();
+
+  if (warp >= K2P_CONSUMER_WARPS) {
+    // ================= producers: Voigt profile + weights into the stage ring =================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
+    const int pw = warp - K2P_CONSUMER_WARPS, pair = pw >> 1, h = 32 * (pw & 1) + lane;
+    uint32_t it = 0, tcount = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
+      const int ql = t / nsb, sb = t - ql * nsb;
+      const QuasarDesc d = desc[q0 + ql];
+      const int64_t s = (int64_t)sb * TS + h;
+      const bool real = s < S;
+      const double off = real ? offset_sorted[s] : 0.0;
+      const double N = real ? nhi_sorted[s] : 0.0;
+      const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), off));  // process_qsos.m:163-165
+      const double opz = __dadd_rn(1.0, z);
+      double mult[3], ncw[3];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;  // voigt.c:278-279
+        ncw[j] = -N * g_lines.cwT[j];
+      }
+      const double* lam = padded_wavelengths + d.pad_off;
+      const double2* px = pix4 + 2 * d.pix_off;
+      const double* Bsrc = bmat + d.bmat_off;
+      const int n = d.n, Pm1 = d.P - 1, gfull = n >> 2;
+      const int nchunks = d.npad / K2P_KC;
+      double q0acc = 0.0, ldacc = 0.0, dprod = 1.0;
+      int esum = 0;
+      // phase 1 of raw block b = 2 c + pair: raws 4b .. 4b+3 of this lane's hypothesis into the ring
+      auto phase1 = [&](int c) {
+        const int r0 = 8 * c + 4 * pair;
+        double l4[4], r4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) l4[u] = __ldg(lam + min(r0 + u, Pm1));
+        raw_lane<4>(l4, mult, ncw, N, etab_s, r4);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) ring[((r0 + u) & (KF_RING - 1)) * TS + h] = r4[u];
+      };
+      producer_bar_sync();   // every producer is done with the previous tile's ring
+      phase1(0);
+      for (int c = 0; c < nchunks; ++c, ++it) {
+        const int st = it % KF_STAGES;
+        phase1(c + 1);       // raws 8c+8 .. 8c+15 (indices beyond P-1 are clamped; their values are never used)
+        producer_bar_sync(); // raws up to 8c+15 are in the ring
+        mbar_wait(&empty[st], ((it / KF_STAGES) & 1) ^ 1);
+        double* stage = smem + (size_t)st * KF_STAGE_DOUBLES;
+        if (pw == 0 && lane == 0) {
+          mbar_expect_tx(&full[st], K2P_B_DOUBLES * 8);
+          bulk_g2s(stage + 2 * K2P_W_DOUBLES, Bsrc + (int64_t)c * K2P_B_DOUBLES, K2P_B_DOUBLES * 8, &full[st]);
+        }
+        const int g = 2 * c + pair;            // kept pixels 4g .. 4g+3
+        double win[10];
+#pragma unroll
+        for (int u = 0; u < 10; ++u) win[u] = ring[((4 * g + u) & (KF_RING - 1)) * TS + h];
+        double* wp = stage + pair * (TS * 4) + h * 4;
+        double* up = wp + K2P_W_DOUBLES;
+        if (g < gfull) weights_lane<false>(win, g, n, 0, px, wp, up, q0acc, ldacc, dprod, esum);
+        else weights_lane<true>(win, g, n, 0, px, wp, up, q0acc, ldacc, dprod, esum);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[st]);
+      }
+      ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
+      double* ax = auxs + (((tcount & 1) * 2 + pair) * TS + h) * 2;
+      ax[0] = q0acc;
+      ax[1] = ldacc;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&auxbar[tcount & 1]);
+    }
+    return;
+  }
+
+  // ================= DMMA warps (as contract_chol_persistent_kernel) =================
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
+  const int mrow = warp & 3, half = warp >> 2;
+  constexpr int TPW = NT / 2;
+  uint32_t it = 0, tcount = 0;
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
+    const int ql = t / nsb, sb = t - ql * nsb;
+    const int n = desc[q0 + ql].n;
+    const int nchunks = desc[q0 + ql].npad / K2P_KC;
+    double acc[TPW][4];
+#pragma unroll
+    for (int j = 0; j < TPW; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0;
+    for (int c = 0; c < nchunks; ++c, ++it) {
+      const int st = it % KF_STAGES;
+      mbar_wait(&full[st], (it / KF_STAGES) & 1);
+      const double* Ws = smem + (size_t)st * KF_STAGE_DOUBLES;
+      const double* Us = Ws + K2P_W_DOUBLES;
+      const double* Bs = Us + K2P_W_DOUBLES;
+#pragma unroll
+      for (int kc = 0; kc < K2P_KC / 4; ++kc) {
+        const double aw0 = Ws[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+        const double aw1 = Ws[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+        const double* bp = Bs + kc * (NCOL * 4) + (half * TPW) * 32 + lane;
+        if (half == 0) {
+#pragma unroll
+          for (int j = 0; j < TPW; ++j) {
+            const double b = bp[j * 32];
+            dmma884(acc[j][0], acc[j][1], aw0, b);
+            dmma884(acc[j][2], acc[j][3], aw1, b);
+          }
+        } else {
+          const double au0 = Us[kc * (TS * 4) + (2 * mrow) * 32 + lane];
+          const double au1 = Us[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
+#pragma unroll
+          for (int j = 0; j < TPW; ++j) {
+            const double b = bp[j * 32];
+            const bool isv = (TPW + j) >= PHI_TILES;
+            dmma884(acc[j][0], acc[j][1], isv ? au0 : aw0, b);
+            dmma884(acc[j][2], acc[j][3], isv ? au1 : aw1, b);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[st]);
+    }
+    {
+      const int r0 = (2 * mrow) * 8 + (lane >> 2);
+      const int cbase = (half * TPW) * 8 + 2 * (lane & 3);
+#pragma unroll
+      for (int j = 0; j < TPW; ++j) {
+        double* p0 = Cs + (size_t)r0 * LDC + cbase + j * 8;
+        double* p1 = p0 + 8 * LDC;
+        p0[0] = acc[j][0]; p0[1] = acc[j][1];
+        p1[0] = acc[j][2]; p1[1] = acc[j][3];
+      }
+    }
+    consumer_bar_sync();
+    {
+      const int srow = tid >> 2, q4 = tid & 3;
+      const int64_t s = (int64_t)sb * TS + srow;
+      mbar_wait(&auxbar[tcount & 1], (tcount >> 1) & 1);
+      const double* a0 = auxs + (((tcount & 1) * 2 + 0) * TS + srow) * 2;
+      const double* a1 = auxs + (((tcount & 1) * 2 + 1) * TS + srow) * 2;
+      const double q0v = a0[0] + a1[0], ldv = a0[1] + a1[1];
+      const double lp = chol_logp_quad<true>(Cs + (size_t)srow * LDC, k, q4, q0v, ldv, n);
+      if (q4 == 0) {
+        if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
+        else if (s == S) ll_no_dla[q0 + ql] = lp;
+      }
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
 // Generic-rank path (20 < k <= KGEN_MAX; BASELINE config 5 is k = 40 on 2433 pixels).
 // The accumulator tile of one sample block no longer fits the register file (k = 40: 860 columns),
 // so the contraction runs per COLUMN BLOCK of <= 30 eight-column tiles: grid = (tiles, column
