@@ -1,17 +1,24 @@
-// kernels.cuh -- the four sm_100a kernels of the DLA model-evaluation hot path.
+// kernels.cuh -- the sm_100a kernels of the DLA model-evaluation hot path and of its neighbours.
 //
-//   K0 build_bmat_kernel   per quasar: B = [vech(M_p M_p^T) | M_p] in DMMA-fragment order
-//   K1 voigt_weights_kernel  voigt.c:278-299 + process_qsos.m:163-165,:189-193: per (sample,pixel)
-//                            a, then w = a^2/d, u = a r/d written in DMMA-fragment order,
-//                            and the row reductions q0 = sum r^2/d, ld = sum log d
-//   K2 contract_chol_kernel  log_mvnpdf_low_rank.m:22-32 recast: G = W.Phi, v = U.M on FP64
-//                            tensor cores (DMMA.8x8x4), operands staged by 1-D TMA bulk copies
-//                            (cp.async.bulk + mbarrier), then the per-sample 20x20 Cholesky,
-//                            log-det and quadratic form in shared memory
-//   K3 reduce_kernel       process_qsos.m:202-212, :223-229, generate_ascii_catalog.m:73
+// Product path (k <= 20, the as-written gather, 3 Lyman lines):
+//   K0 build_bmat_kernel, pack_pixels_kernel   per quasar: B = [vech(M_p M_p^T) | M_p] in DMMA-fragment
+//                            order; {omega2, noise, mu, flux} records
+//   K1 voigt_weights_lane_kernel   voigt.c:278-299 + process_qsos.m:163-165,:189-193: a lane owns one
+//                            hypothesis (z-sorted set) and walks a spectrum segment; a, then w = a^2/d,
+//                            u = a r/d in DMMA-fragment order, partial q0 = sum r^2/d, ld = sum log d
+//   K2 contract_chol_persistent_kernel   log_mvnpdf_low_rank.m:22-32 recast: G = W.Phi, v = U.M on FP64
+//                            tensor cores (DMMA.8x8x4); persistent CTAs, producer warp + TMA bulk copies
+//                            through a full/empty mbarrier ring, setmaxnreg register split, per-sample
+//                            21x21 bordered Cholesky in registers (one quad of lanes per sample)
+//   K3 reduce_kernel         process_qsos.m:202-212, :223-229, generate_ascii_catalog.m:73
+// General / fallback forms: voigt_weights_kernel (masked gathers, num_lines != 3), contract_chol_kernel
+//   (one CTA per tile), contract_block_kernel<TPW> + chol_generic_kernel (20 < k <= 64),
+//   fused_voigt_contract_kernel (opt-in experiment), voigt_single_kernel (the MEX seam).
+// Neighbours of the path: prep_model_kernel (process_qsos.m:102-147 on the device),
+//   train_*_kernel (objective.m / spectrum_loss.m).
 //
-// Geometry shared by all kernels (see DESIGN.md "Data layout in HBM"):
-//   TS  = 64 samples per sample block (one K2 CTA tile), KC = 16 pixels per K-chunk,
+// Geometry shared by the kernels (see DESIGN.md "Data layout in HBM"):
+//   TS  = 64 samples per sample block (one K2 tile), pixels padded to a multiple of KC = 16,
 //   NCOL = 240 B-columns = 27 tiles of 8 for vech(B) (210 used at k=20) + 3 tiles for M.
 //   W,U : [sample block][pixel/4][64 samples][4 pixels]   (an 8x4 DMMA A-fragment = 256 contiguous B)
 //   Bmat: [pixel/4][240 columns][4 pixels]                (a 4x8 DMMA B-fragment = 256 contiguous B)
