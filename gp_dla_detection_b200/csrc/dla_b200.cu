@@ -124,7 +124,7 @@ struct dla_ctx {
   DevBuf d_desc, d_padded, d_pidx, d_flux, d_mu, d_om, d_nv, d_M, d_pix4;
   DevBuf d_sample_ll, d_ll_no, d_ll_dla, d_lp_no, d_lp_dla, d_post, d_map;
   // chunk workspace
-  DevBuf d_W, d_U, d_bmat, d_aux, d_ll_chunk, d_G;
+  DevBuf d_W, d_U, d_bmat, d_aux, d_ll_chunk, d_G, d_krank;
   dla_timing timing{};
 };
 
@@ -219,6 +219,22 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     if (smem > 100 * 1024) BAD_ARG(c, "a quasar has too many pixels for the Voigt kernel's shared-memory staging");
     dla::voigt_weights_lane_kernel<<<(unsigned)((int64_t)ch.nq * nsb * nseg), dla::K1S_THREADS, smem, st>>>(
         in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_etab256.as<double>(), W, U, aux, lam_cap, nseg);
+  } else if (num_lines == 3 && !c->force_pixel_lane_k1) {
+    // masked gather (profile_index[j] != j for some quasar of the chunk): lane kernel over profile positions
+    {
+      dim3 grid((unsigned)((ch.max_P - 5 + 255) / 256), (unsigned)ch.nq);
+      dla::kept_rank_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.pidx, c->d_krank.as<int32_t>());
+    }
+    const int ngrp = (ch.max_P - 6 + 3) / 4;
+    nseg = std::min(dla::K1S_NSEG_MAX, std::max(dla::K1S_NSEG_MIN, (ngrp + 79) / 80));
+    const int gmax = (ngrp + nseg - 1) / nseg + 1;
+    const int lam_cap = 4 * gmax + 8, px_cap = 4 * gmax;
+    const size_t smem = ((size_t)lam_cap + 4 * (size_t)px_cap) * 8 + ((size_t)4 * gmax + 2) * 4;
+    if (smem > 100 * 1024) BAD_ARG(c, "a quasar has too many pixels for the Voigt kernel's shared-memory staging");
+    dla::voigt_weights_lane_gather_kernel<<<(unsigned)((int64_t)ch.nq * nsb * nseg), dla::K1S_THREADS, smem, st>>>(
+        in.desc, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_krank.as<int32_t>(),
+        c->d_etab256.as<double>(), W, U, aux, lam_cap, px_cap, nseg);
+    c->timing.launches += 1;
   } else {
     const int raw_stride = (int)round_up(ch.max_P, 2) + 2;  // +2: the 16-byte window loads of the tail may touch one double past P
     const int warps = k1_warps_for(raw_stride);
@@ -463,6 +479,7 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
   CREATE_TRY(cudaFuncSetAttribute(dla::chol_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)dla::chg_smem_bytes(dla::KGEN_MAX)));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_lane_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
   CREATE_TRY(cudaFuncSetAttribute(dla::voigt_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #undef CREATE_TRY
   *out = c;
@@ -475,7 +492,7 @@ void dla_destroy(dla_ctx* c) {
   cudaStreamSynchronize(c->stream);
   for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_perm, &c->d_etab256, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
                     &c->d_nv, &c->d_M, &c->d_pix4, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
-                    &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk, &c->d_G,
+                    &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk, &c->d_G, &c->d_krank,
                     &c->d_mrest, &c->d_mmu, &c->d_mM, &c->d_mlo, &c->d_lamk, &c->d_zq,
                     &c->t_y, &c->t_l, &c->t_nv, &c->t_x, &c->t_om2, &c->t_aux, &c->t_E, &c->t_fq, &c->t_beta, &c->t_P,
                     &c->t_A1, &c->t_S, &c->t_gp, &c->t_g, &c->t_gsc, &c->t_desc})
@@ -606,6 +623,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
   CU_TRY(c, need(c->d_desc, (size_t)Q * sizeof(QuasarDesc)));
   CU_TRY(c, need(c->d_padded, (size_t)npadtot * 8));
   CU_TRY(c, need(c->d_pidx, (size_t)npix * 4));
+  CU_TRY(c, need(c->d_krank, (size_t)npadtot * 4));
   CU_TRY(c, need(c->d_pix4, (size_t)npix * 32));
   CU_TRY(c, need(c->d_flux, (size_t)npix * 8));
   CU_TRY(c, need(c->d_mu, (size_t)npix * 8));

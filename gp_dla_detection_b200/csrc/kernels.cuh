@@ -775,6 +775,170 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
   auxq[(int64_t)(nseg + seg) * S_pad + s] = ldacc;
 }
 
+// ----------------------------------------------------------------------------------------------
+// K1, sample-per-lane form for MASKED gathers (profile_index[j] != j: the "intended" mask mode,
+// process_qsos.m:180/:189 with the gather fixed).  The lane walks PROFILE positions; a position that
+// is kept (warp-uniform: the mask belongs to the quasar) yields one (w, u) pair, staged in a 64-byte
+// per-lane shared-memory slot and flushed as 32-byte records when four kept pixels are complete, so
+// the stores keep the fragment layout's coalescing.  krank[i] = number of kept positions < i.
+// ----------------------------------------------------------------------------------------------
+__global__ void kept_rank_kernel(const QuasarDesc* __restrict__ desc, int q0, const int32_t* __restrict__ profile_index,
+                                 int32_t* __restrict__ krank /* at pad_off: P_q entries per quasar (n_full + 1 used) */) {
+  const QuasarDesc d = desc[q0 + blockIdx.y];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n_full = d.P - 6;
+  if (i > n_full) return;
+  const int32_t* pi = profile_index + d.pix_off;
+  int lo = 0, hi = d.n;  // first kept index whose position is >= i
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (pi[mid] < i) lo = mid + 1; else hi = mid;
+  }
+  krank[d.pad_off + i] = lo;
+}
+
+__global__ void __launch_bounds__(K1S_THREADS, 8)
+voigt_weights_lane_gather_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
+                                 const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
+                                 const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
+                                 const int32_t* __restrict__ krank, const double* __restrict__ etab256,
+                                 double* __restrict__ Wbuf, double* __restrict__ Ubuf, double* __restrict__ aux,
+                                 int lam_cap, int px_cap, int nseg) {
+  extern __shared__ __align__(16) double k1s_smem[];
+  __shared__ double etab_s[256];
+  __shared__ __align__(16) double stage_s[K1S_THREADS][8];   // per lane: w[4], u[4]
+  const int seg = blockIdx.x % nseg;
+  const int tile = blockIdx.x / nseg;
+  const int ql = tile / nsb, sb = tile % nsb;
+  const QuasarDesc d = desc[q0 + ql];
+  const int tid = threadIdx.x;
+  const int n_full = d.P - 6, n = d.n, npad = d.npad, npc = npad >> 2;
+  const int ngrp = (n_full + 3) >> 2;                         // groups of 4 profile positions
+  const int g0 = (int)(((int64_t)seg * ngrp) / nseg), g1 = (int)(((int64_t)(seg + 1) * ngrp) / nseg);
+  const int i0 = 4 * g0, i1 = min(4 * g1, n_full);            // profile positions of this segment
+  const int32_t* kr = krank + d.pad_off;
+  const int k0 = kr[i0], k1 = kr[i1];                          // kept pixels this segment emits: [k0, k1)
+  const bool last = (seg == nseg - 1);
+  const int lbase = max(i0 - 2, 0), llast = min(4 * g1 + 5, d.P - 1);
+  double* lam_s = k1s_smem;
+  double2* px_s = reinterpret_cast<double2*>(k1s_smem + lam_cap);
+  int32_t* kr_s = reinterpret_cast<int32_t*>(k1s_smem + lam_cap + 4 * px_cap);
+  for (int i = tid; i < 256; i += K1S_THREADS) etab_s[i] = etab256[i];
+  {
+    const double* lam_g = padded_wavelengths + d.pad_off + lbase;
+    for (int i = tid; i <= llast - lbase; i += K1S_THREADS) lam_s[i] = __ldg(lam_g + i);
+    const double2* px_g = pix4 + 2 * (d.pix_off + k0);
+    for (int i = tid; i < 2 * (k1 - k0); i += K1S_THREADS) px_s[i] = __ldg(px_g + i);
+    for (int i = tid; i <= i1 - i0; i += K1S_THREADS) kr_s[i] = kr[i0 + i];
+  }
+  __syncthreads();
+  const int srow = tid;
+  const int64_t s = (int64_t)sb * TS + srow;
+  const bool real = s < S;
+  const double off = real ? offset_sorted[s] : 0.0;
+  const double N = real ? nhi_sorted[s] : 0.0;
+  const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), off));
+  const double opz = __dadd_rn(1.0, z);
+  double mult[3], ncw[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
+    ncw[j] = -N * g_lines.cwT[j];
+  }
+  const double* lam = lam_s - lbase;
+  const double2* px = px_s - 2 * k0;
+  const int64_t S_pad = (int64_t)nsb * TS;
+  double* Wt = Wbuf + d.wu_off + (int64_t)sb * npc * (TS * 4) + srow * 4;   // + group * TS * 4
+  double* Ut = Ubuf + d.wu_off + (int64_t)sb * npc * (TS * 4) + srow * 4;
+  double* st = stage_s[tid];
+
+  double q0acc = 0.0, ldacc = 0.0, dprod = 1.0;
+  int esum = 0;
+  int kout = k0, fill = k0 & 3;       // next kept index; entries of the current group already staged
+  const int first_lo = fill;          // the first group of the segment may start mid-group
+  bool first_group = true;
+  // emit one (w, u): stage, and flush a completed group of four (warp-uniform control flow)
+  auto emit = [&](double w, double u) {
+    st[fill] = w;
+    st[4 + fill] = u;
+    ++fill;
+    ++kout;
+    if (fill == 4) {
+      double* wp = Wt + (int64_t)((kout - 1) >> 2) * (TS * 4);
+      double* up = Ut + (int64_t)((kout - 1) >> 2) * (TS * 4);
+      if (first_group && first_lo != 0) {     // shared with the previous segment: only our entries
+        for (int e = first_lo; e < 4; ++e) { wp[e] = st[e]; up[e] = st[4 + e]; }
+      } else {
+        reinterpret_cast<double2*>(wp)[0] = *reinterpret_cast<const double2*>(st);
+        reinterpret_cast<double2*>(wp)[1] = *reinterpret_cast<const double2*>(st + 2);
+        reinterpret_cast<double2*>(up)[0] = *reinterpret_cast<const double2*>(st + 4);
+        reinterpret_cast<double2*>(up)[1] = *reinterpret_cast<const double2*>(st + 6);
+      }
+      first_group = false;
+      fill = 0;
+    }
+  };
+  double win[10];
+#pragma unroll
+  for (int t = 0; t < 10; ++t) win[t] = 0.0;
+  const int nsteps = g1 - g0 + 2;
+  for (int stp = 0; stp < nsteps; ++stp) {
+    const int b = 4 * (g0 + stp) - 2;
+    double l4[4], r4[4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) l4[h] = lam[min(max(b + h, lbase), llast)];
+    raw_lane<4>(l4, mult, ncw, N, etab_s, r4);
+#pragma unroll
+    for (int t = 0; t < 6; ++t) win[t] = win[t + 4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) win[6 + h] = r4[h];
+    if (stp >= 2) {
+      const int ib = 4 * (g0 + stp - 2);       // profile positions ib .. ib+3
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const int i = ib + h;
+        if (i < i1 && kr_s[i - i0 + 1] != kr_s[i - i0]) {   // kept (warp-uniform)
+          const int kk = kr_s[i - i0];
+          const double2 p01 = px[2 * kk], p23 = px[2 * kk + 1];
+          double a = 0.0;
+#pragma unroll
+          for (int t = 0; t < 7; ++t) a = fma(win[h + t], dla_instrument_profile[t], a);
+          const double a2 = a * a;
+          const double d_ = fma(p01.x, a2, p01.y);
+          const double r = fma(-p23.x, a, p23.y);
+          const double rinv = rcp_cubic(d_);
+          const double gq_ = a * rinv;
+          const double rr = r * rinv;
+          q0acc = fma(r, rr, q0acc);
+          const bool ok = (unsigned)(__double2hiint(d_) - ((1023 - 200) << 20)) < (unsigned)(400 << 20);
+          if (ok) {
+            dprod *= d_;
+            const int hi = __double2hiint(dprod);
+            const int e = (hi >> 20) - 1023;
+            esum += e;
+            dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
+          } else {
+            ldacc += log(d_);
+          }
+          emit(a * gq_, r * gq_);
+        }
+      }
+    }
+  }
+  if (last) {  // zero padding of the kept-pixel axis up to npad
+    while (kout < npad) emit(0.0, 0.0);
+  } else if (fill != 0) {  // the group continues in the next segment: write our entries only
+    double* wp = Wt + (int64_t)(kout >> 2) * (TS * 4);
+    double* up = Ut + (int64_t)(kout >> 2) * (TS * 4);
+    const int lo = (first_group ? first_lo : 0);
+    for (int e = lo; e < fill; ++e) { wp[e] = st[e]; up[e] = st[4 + e]; }
+  }
+  ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
+  double* auxq = aux + (int64_t)ql * 2 * nseg * S_pad;
+  auxq[(int64_t)seg * S_pad + s] = q0acc;
+  auxq[(int64_t)(nseg + seg) * S_pad + s] = ldacc;
+}
+
 // Single-profile seam (dla_voigt = the voigt MEX, voigt.c:253-304). One CTA.
 __global__ void voigt_single_kernel(const double* __restrict__ lambdas, int num_points, double z, double N,
                                     int num_lines, double* __restrict__ raw, double* __restrict__ profile) {
