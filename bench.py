@@ -41,6 +41,9 @@ WORKLOADS = {
                 "name": "BASELINE config 4 shape (dense prior sampling, 100000 hypotheses)"},
     "config5": {"k": 40, "dlambda": 0.125, "ragged": False, "samples": 10000, "pixels": 2433,
                 "name": "BASELINE config 5 shape (stressed contraction, k=40 on the 0.125 A grid)"},
+    # side measurement of the training objective (objective.m); --quasars = training quasars
+    "train": {"k": 20, "dlambda": 0.25, "ragged": False, "samples": 0, "pixels": 1217,
+              "name": "training objective f+g (objective.m / spectrum_loss.m)"},
 }
 
 
@@ -397,8 +400,47 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_train(args):
+    """Side measurement, not the bench line: evaluations of the training objective on one B200 against the
+    numpy restatement of objective.m (the checker) on a bounded sample of the same training set."""
+    from gp_dla_detection_b200 import synthetic
+    from gp_dla_detection_b200.learn_qso_model import TrainingObjective
+    Q = args.quasars
+    x, y, l1, nv = synthetic.make_training_set(Q, k=K_RANK, n_rest=N_PIX, seed=11)
+    obj = TrainingObjective(y, l1, nv, K_RANK)
+    for _ in range(max(1, args.warmup)):
+        f, g = obj(x)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        f, g = obj(x)
+    dt = (time.perf_counter() - t) / args.steps
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import train_oracle as T
+        qs = min(Q, 40)
+        t = time.perf_counter()
+        fr, gr = T.objective(x, y[:qs], l1[:qs], nv[:qs], apply_priors=False)
+        dtc = time.perf_counter() - t
+        sub = TrainingObjective(y[:qs], l1[:qs], nv[:qs], K_RANK)
+        fl, gl = sub.local(x)
+        sub.close()
+        cpu = {"value": qs / dtc, "unit": "training quasars/sec", "cores": 1, "kind": "port",
+               "sample": f"{qs} quasars, numpy restatement of objective.m",
+               "f_rel_err_on_sample": abs(fl - fr) / abs(fr),
+               "g_err_over_scale_on_sample": float(np.max(np.abs(gl - gr)) / np.max(np.abs(gr)))}
+    obj.close()
+    print(json.dumps({"metric": "training quasars/sec", "value": Q / dt, "unit": "training quasars/sec", "n_gpus": 1,
+                      "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt, "higher_is_better": True,
+                      "dtype": "f64", "data": "synthetic",
+                      "config": {"workload": WORKLOADS["train"]["name"], "quasars": Q, "pixels": N_PIX, "k": K_RANK},
+                      "timed": "wall clock around dla_train_objective (x H2D, f/g D2H inside)", "cpu_baseline": cpu}),
+          flush=True)
+
+
 def main():
     args = parse_args()
+    if args.workload == "train":
+        return run_train(args)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -84,29 +84,4 @@ def dense_nlog_p(y, lya_1pz, noise_variance, M, omega2, c_0, tau_0, beta):
     return 0.5 * (a @ a + 2 * np.sum(np.log(np.diag(Lc))) + y.shape[0] * LOG_2PI)
 
 
-def make_training_set(num_quasars, k=20, n_rest=1217, seed=20260010, missing=0.15):
-    """Synthetic stand-in for learn_qso_model.m:29-75: centred rest-frame fluxes on the model grid with NaN
-    where a spectrum does not cover / is masked, (1 + z_Lya) per pixel, noise variances; and an x vector."""
-    rng = np.random.default_rng(seed)
-    rest = 911.75 + 0.25 * (1217 / n_rest) * np.arange(n_rest)
-    z = rng.uniform(2.15, 5.0, num_quasars)
-    l1pz = (rest[None, :] * (1 + z[:, None])) / 1215.6701
-    M = np.stack([0.35 * (j + 1) ** -0.7 * np.cos(np.pi * (j + 0.5) * np.arange(n_rest) / n_rest + rng.uniform(0, 6.28))
-                  for j in range(k)], axis=1)
-    log_omega = np.log(0.12 + 0.08 * np.sin(np.pi * np.arange(n_rest) / 360) ** 2)
-    nv = np.clip(np.exp(rng.normal(np.log(0.05), 0.7, (num_quasars, n_rest))), 1e-3, 4.0)
-    c0, t0, b = 0.1, 0.0023, 3.65
-    d = nv + np.exp(2 * log_omega)[None, :] * (1 - np.exp(-t0 * l1pz ** b) + c0) ** 2
-    y = (rng.standard_normal((num_quasars, k)) @ M.T) + np.sqrt(d) * rng.standard_normal((num_quasars, n_rest))
-    # missing data: a blue cut per quasar plus random masked runs (NaN in all three arrays, as :36-37, :57-60)
-    for q in range(num_quasars):
-        cut = int(rng.uniform(0, 0.4) * n_rest)
-        bad = np.zeros(n_rest, bool)
-        bad[:cut] = True
-        bad |= rng.random(n_rest) < missing * rng.random()
-        y[q, bad] = np.nan
-        l1pz[q, bad] = np.nan
-        nv[q, bad] = np.nan
-    x = np.concatenate([(M * (1 + 0.05 * rng.standard_normal(M.shape))).ravel(order="F"),
-                        log_omega + 0.05 * rng.standard_normal(n_rest), [np.log(0.11), np.log(0.0025), np.log(3.5)]])
-    return x, y, l1pz, nv
+from gp_dla_detection_b200.synthetic import make_training_set  # noqa: E402,F401  (synthetic inputs live in the package)
