@@ -47,7 +47,8 @@ def is_stale() -> bool:
 def build_library(force: bool = False, verbose: bool = False) -> str:
     if not force and not is_stale():
         return LIB_PATH
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH, *[os.path.join(CSRC, s) for s in SOURCES]]
+    extra = os.environ.get("DLA_NVCC_EXTRA", "").split()   # tuning builds only (e.g. -DDLA_K2P_KC=16 -DDLA_K2P_STAGES=2)
+    cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-o", LIB_PATH, *[os.path.join(CSRC, s) for s in SOURCES]]
     env = dict(os.environ)
     env.pop("CC", None)  # the image's CC=/opt/gcc/bin/gcc is not a usable host compiler for nvcc
     env.pop("CXX", None)

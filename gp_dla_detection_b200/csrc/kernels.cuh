@@ -1189,8 +1189,16 @@ contract_chol_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64
 // main loop, and the first chunks of the next tile are already in flight while the current tile
 // runs its Cholesky epilogue out of a dedicated C buffer.
 // ----------------------------------------------------------------------------------------------
-constexpr int K2P_KC = 8;                                  // pixels per stage
-constexpr int K2P_STAGES = 4;
+#ifndef DLA_K2P_KC
+#define DLA_K2P_KC 8
+#define DLA_K2P_STAGES 4
+#endif
+#ifndef DLA_K2P_PREFETCH
+#define DLA_K2P_PREFETCH 0   // fragment double buffering in the persistent contraction (needs DLA_K2P_KC == 8);
+                             // measured: no gain (11.11 vs 11.09 ms), the LDS waits were already hidden by the second warp
+#endif
+constexpr int K2P_KC = DLA_K2P_KC;                         // pixels per stage
+constexpr int K2P_STAGES = DLA_K2P_STAGES;
 constexpr int K2P_W_DOUBLES = TS * K2P_KC;                 // 512
 constexpr int K2P_B_DOUBLES = K2P_KC * NCOL;               // 1920
 constexpr int K2P_STAGE_DOUBLES = 2 * K2P_W_DOUBLES + K2P_B_DOUBLES;  // 2944 = 23552 B
@@ -1231,7 +1239,7 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
   // 384 threads x 168 registers fill the register file; the producer's warpgroup hands most of its
   // share back so that the DMMA warps can hold the accumulator tile and the register-resident Cholesky
   if (warp >= K2P_CONSUMER_WARPS) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
     // ---------------- producer ----------------
     if (warp == K2P_CONSUMER_WARPS && lane == 0) {
       uint32_t it = 0;
@@ -1259,7 +1267,11 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
   }
 
   // ---------------- DMMA warps: 4 row groups of 16 samples x 2 column halves of 15 tiles ----------------
+#if DLA_K2P_PREFETCH
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+#else
   asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+#endif
   const int mrow = warp & 3, half = warp >> 2;
   constexpr int TPW = NT / 2;
   uint32_t it = 0;
@@ -1271,6 +1283,52 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
 #pragma unroll
     for (int j = 0; j < TPW; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0;
 
+#if DLA_K2P_PREFETCH
+    // Fragment double buffering: the A/B fragments of the NEXT 4-pixel step (the other half of this chunk, or
+    // the first half of the next chunk) are loaded before the 30 DMMAs of the current step issue, so a warp
+    // never sits on a shared-memory load with the tensor pipe idle.  Two register sets (X for the first half
+    // of a chunk, Y for the second) alternate without moves.
+    static_assert(K2P_KC == 8, "fragment double buffering is written for two 4-pixel steps per stage");
+    double xw0, xw1, xu0 = 0.0, xu1 = 0.0, xb[TPW], yw0, yw1, yu0 = 0.0, yu1 = 0.0, yb[TPW];
+#define K2P_LOAD(P, stage_, kc_)                                                                   \
+    {                                                                                              \
+      const double* Ws_ = smem + (size_t)(stage_) * K2P_STAGE_DOUBLES + (kc_) * (TS * 4) + (2 * mrow) * 32 + lane; \
+      P##w0 = Ws_[0];                                                                              \
+      P##w1 = Ws_[32];                                                                             \
+      if (half) { P##u0 = Ws_[K2P_W_DOUBLES]; P##u1 = Ws_[K2P_W_DOUBLES + 32]; }                   \
+      const double* bp_ = smem + (size_t)(stage_) * K2P_STAGE_DOUBLES + 2 * K2P_W_DOUBLES + (kc_) * (NCOL * 4) + \
+                          (half * TPW) * 32 + lane;                                                \
+      _Pragma("unroll") for (int j = 0; j < TPW; ++j) P##b[j] = bp_[j * 32];                       \
+    }
+#define K2P_MMA(P)                                                                                 \
+    {                                                                                              \
+      _Pragma("unroll") for (int j = 0; j < TPW; ++j) {                                            \
+        const bool isv = half && (TPW + j) >= PHI_TILES;                                           \
+        dmma884(acc[j][0], acc[j][1], isv ? P##u0 : P##w0, P##b[j]);                               \
+        dmma884(acc[j][2], acc[j][3], isv ? P##u1 : P##w1, P##b[j]);                               \
+      }                                                                                            \
+    }
+    {
+      const int st0 = it % K2P_STAGES;
+      mbar_wait(&full[st0], (it / K2P_STAGES) & 1);
+      K2P_LOAD(x, st0, 0)
+    }
+    for (int c = 0; c < nchunks; ++c, ++it) {
+      const int st = it % K2P_STAGES;
+      K2P_LOAD(y, st, 1)
+      K2P_MMA(x)
+      if (c + 1 < nchunks) {
+        const int st1 = (it + 1) % K2P_STAGES;
+        mbar_wait(&full[st1], ((it + 1) / K2P_STAGES) & 1);
+        K2P_LOAD(x, st1, 0)
+      }
+      K2P_MMA(y)      // every load of stage st has been consumed by an issued DMMA once this has run
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[st]);
+    }
+#undef K2P_LOAD
+#undef K2P_MMA
+#else
     for (int c = 0; c < nchunks; ++c, ++it) {
       const int st = it % K2P_STAGES;
       mbar_wait(&full[st], (it / K2P_STAGES) & 1);
@@ -1304,6 +1362,8 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[st]);
     }
+
+#endif
 
     // accumulators -> C tile (its readers of the previous tile passed the barrier below)
     {
@@ -1347,7 +1407,9 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
 constexpr int KF_STAGES = 3;
 constexpr int KF_RING = 32;                                       // raw-transmission ring, pixels
 constexpr int KF_THREADS = 384;                                   // 8 DMMA warps + 4 producer warps
-constexpr int KF_STAGE_DOUBLES = K2P_STAGE_DOUBLES;               // W 512 | U 512 | B 1920
+constexpr int KF_KC = 8;                                          // pixels per stage (the phase structure assumes 8)
+constexpr int KF_W_DOUBLES = TS * KF_KC, KF_B_DOUBLES = KF_KC * NCOL;
+constexpr int KF_STAGE_DOUBLES = 2 * KF_W_DOUBLES + KF_B_DOUBLES;  // W 512 | U 512 | B 1920
 constexpr size_t KF_SMEM_DOUBLES = (size_t)KF_STAGES * KF_STAGE_DOUBLES + K2P_C_DOUBLES + KF_RING * TS +
                                    2 * 2 * TS * 2 + 256;
 constexpr size_t KF_SMEM_BYTES = KF_SMEM_DOUBLES * 8 + (2 * KF_STAGES + 2) * 8;
@@ -1408,7 +1470,7 @@ fused_voigt_contract_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb
       const double2* px = pix4 + 2 * d.pix_off;
       const double* Bsrc = bmat + d.bmat_off;
       const int n = d.n, Pm1 = d.P - 1, gfull = n >> 2;
-      const int nchunks = d.npad / K2P_KC;
+      const int nchunks = d.npad / KF_KC;
       double q0acc = 0.0, ldacc = 0.0, dprod = 1.0;
       int esum = 0;
       // phase 1 of raw block b = 2 c + pair: raws 4b .. 4b+3 of this lane's hypothesis into the ring
@@ -1430,15 +1492,15 @@ fused_voigt_contract_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb
         mbar_wait(&empty[st], ((it / KF_STAGES) & 1) ^ 1);
         double* stage = smem + (size_t)st * KF_STAGE_DOUBLES;
         if (pw == 0 && lane == 0) {
-          mbar_expect_tx(&full[st], K2P_B_DOUBLES * 8);
-          bulk_g2s(stage + 2 * K2P_W_DOUBLES, Bsrc + (int64_t)c * K2P_B_DOUBLES, K2P_B_DOUBLES * 8, &full[st]);
+          mbar_expect_tx(&full[st], KF_B_DOUBLES * 8);
+          bulk_g2s(stage + 2 * KF_W_DOUBLES, Bsrc + (int64_t)c * KF_B_DOUBLES, KF_B_DOUBLES * 8, &full[st]);
         }
         const int g = 2 * c + pair;            // kept pixels 4g .. 4g+3
         double win[10];
 #pragma unroll
         for (int u = 0; u < 10; ++u) win[u] = ring[((4 * g + u) & (KF_RING - 1)) * TS + h];
         double* wp = stage + pair * (TS * 4) + h * 4;
-        double* up = wp + K2P_W_DOUBLES;
+        double* up = wp + KF_W_DOUBLES;
         if (g < gfull) weights_lane<false>(win, g, n, 0, px, wp, up, q0acc, ldacc, dprod, esum);
         else weights_lane<true>(win, g, n, 0, px, wp, up, q0acc, ldacc, dprod, esum);
         __syncwarp();
@@ -1462,7 +1524,7 @@ fused_voigt_contract_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
     const int ql = t / nsb, sb = t - ql * nsb;
     const int n = desc[q0 + ql].n;
-    const int nchunks = desc[q0 + ql].npad / K2P_KC;
+    const int nchunks = desc[q0 + ql].npad / KF_KC;
     double acc[TPW][4];
 #pragma unroll
     for (int j = 0; j < TPW; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0;
@@ -1470,10 +1532,10 @@ fused_voigt_contract_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb
       const int st = it % KF_STAGES;
       mbar_wait(&full[st], (it / KF_STAGES) & 1);
       const double* Ws = smem + (size_t)st * KF_STAGE_DOUBLES;
-      const double* Us = Ws + K2P_W_DOUBLES;
-      const double* Bs = Us + K2P_W_DOUBLES;
+      const double* Us = Ws + KF_W_DOUBLES;
+      const double* Bs = Us + KF_W_DOUBLES;
 #pragma unroll
-      for (int kc = 0; kc < K2P_KC / 4; ++kc) {
+      for (int kc = 0; kc < KF_KC / 4; ++kc) {
         const double aw0 = Ws[kc * (TS * 4) + (2 * mrow) * 32 + lane];
         const double aw1 = Ws[kc * (TS * 4) + (2 * mrow + 1) * 32 + lane];
         const double* bp = Bs + kc * (NCOL * 4) + (half * TPW) * 32 + lane;
