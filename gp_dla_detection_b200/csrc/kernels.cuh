@@ -692,7 +692,10 @@ __device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int
   reinterpret_cast<double2*>(up)[1] = make_double2(u[2], u[3]);
 }
 
-__global__ void __launch_bounds__(K1S_THREADS, 8)
+#ifndef DLA_K1S_MINB
+#define DLA_K1S_MINB 8   // resident CTAs per SM the lane kernel is compiled for (8 -> 128 registers)
+#endif
+__global__ void __launch_bounds__(K1S_THREADS, DLA_K1S_MINB)
 voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int64_t S,
                           const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
                           const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
