@@ -114,6 +114,7 @@ struct dla_ctx {
   bool have_samples = false;
   bool force_pixel_lane_k1 = false;  // DLA_B200_K1=pixel: always use voigt_weights_kernel
   bool force_tile_k2 = false;        // DLA_B200_K2=tile: one CTA per tile (contract_chol_kernel)
+  bool k2_rowsplit = false;          // DLA_B200_K2=rowsplit: contract_chol_rowsplit_kernel
   bool use_fused = false;            // DLA_B200_FUSED=1: fused_voigt_contract_kernel (W/U never leave the SM)
   int num_sms = 148;
   // staged batch
@@ -263,8 +264,12 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   } else if (!c->force_tile_k2) {
     const int64_t ntiles = (int64_t)ch.nq * nsb;
     const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
-    dla::contract_chol_persistent_kernel<<<grid, dla::K2P_THREADS, dla::K2P_SMEM_BYTES, st>>>(
-        in.desc, ch.q0, nsb, (int)ntiles, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k, nseg);
+    if (c->k2_rowsplit)
+      dla::contract_chol_rowsplit_kernel<<<grid, dla::K2P_THREADS, dla::K2P_SMEM_BYTES, st>>>(
+          in.desc, ch.q0, nsb, (int)ntiles, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k, nseg);
+    else
+      dla::contract_chol_persistent_kernel<<<grid, dla::K2P_THREADS, dla::K2P_SMEM_BYTES, st>>>(
+          in.desc, ch.q0, nsb, (int)ntiles, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k, nseg);
   } else {
     const size_t smem = (size_t)dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64;
     dla::contract_chol_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K2_THREADS, smem, st>>>(
@@ -458,6 +463,7 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     c->use_fused = fu && strcmp(fu, "1") == 0;
     const char* k2 = getenv("DLA_B200_K2");
     c->force_tile_k2 = k2 && strcmp(k2, "tile") == 0;
+    c->k2_rowsplit = k2 && strcmp(k2, "rowsplit") == 0;
     c->num_sms = prop.multiProcessorCount;
     const char* k1 = getenv("DLA_B200_K1");
     c->force_pixel_lane_k1 = k1 && strcmp(k1, "pixel") == 0;
@@ -466,6 +472,8 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
   CREATE_TRY(cudaFuncSetAttribute(dla::fused_voigt_contract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)dla::KF_SMEM_BYTES));
+  CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_rowsplit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)dla::K2P_SMEM_BYTES));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)dla::K2P_SMEM_BYTES));
 #define CB_ATTR(T)                                                                                         \

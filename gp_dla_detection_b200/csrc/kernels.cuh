@@ -1021,7 +1021,9 @@ __device__ __forceinline__ int tri(int i, int l) { return ((i * (i + 1)) >> 1) +
 // t = L^-1 v and the corner as q0 - t^T t = r^T K^-1 r; log|B| = sum log pivots
 // (log_mvnpdf_low_rank.m:23-32).  No shared-memory traffic after the initial load.
 // row[0..210): vech(G), row[VOFF..VOFF+k): v.  Returns log p on all four lanes.
-template <bool SYNC_AFTER_LOAD = false>
+// SYNC_AFTER_LOAD: 0 none, 1 the 256-thread named barrier (the C tile is shared by the CTA), 2 __syncwarp
+// (the rows belong to this warp only)
+template <int SYNC_AFTER_LOAD = 0>
 __device__ __forceinline__ double chol_logp_quad(const double* __restrict__ row, int k, int t, double q0, double ld,
                                                  int n) {
   constexpr int NB = KMAX;      // border row index (20)
@@ -1044,7 +1046,8 @@ __device__ __forceinline__ double chol_logp_quad(const double* __restrict__ row,
       A[r][l] = v;
     }
   }
-  if (SYNC_AFTER_LOAD) asm volatile("bar.sync 1, 256;" ::: "memory");  // the C tile may be overwritten from here on
+  if (SYNC_AFTER_LOAD == 1) asm volatile("bar.sync 1, 256;" ::: "memory");  // the C tile may be overwritten from here on
+  if (SYNC_AFTER_LOAD == 2) __syncwarp();
   double pprod = 1.0;  // product of the pivots this lane is responsible for (j = t mod 4): <= 5 factors
 #pragma unroll
   for (int j = 0; j < NB; ++j) {
@@ -1387,7 +1390,109 @@ contract_chol_persistent_kernel(const QuasarDesc* __restrict__ desc, int q0, int
       const int64_t S_pad = (int64_t)nsb * TS;
       double q0v, ldv;
       aux_sums(aux, ql, nseg, S_pad, s, q0v, ldv);
-      const double lp = chol_logp_quad<true>(Cs + (size_t)srow * LDC, k, q4, q0v, ldv, n);
+      const double lp = chol_logp_quad<1>(Cs + (size_t)srow * LDC, k, q4, q0v, ldv, n);
+      if (q4 == 0) {
+        if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
+        else if (s == S) ll_no_dla[q0 + ql] = lp;
+      }
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// K2, persistent, ROW-SPLIT warp tiling: warp w owns sample rows 8w .. 8w+7 and ALL 30 column tiles
+// (60 accumulator doubles per thread, as before).  A warp's eight samples are then complete inside the
+// warp, so the epilogue (C rows through shared memory, one quad of lanes per sample) needs no CTA-wide
+// barrier: warps drift apart by up to the depth of the stage ring and one warp's Cholesky overlaps the
+// other warp's DMMAs on the same sub-partition.  Price: every warp reads all 30 B fragments per 4-pixel
+// step (32 LDS.64 per 30 DMMA instead of 17-19).
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(K2P_THREADS, 1)
+contract_chol_rowsplit_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, int ntiles, int64_t S,
+                              const double* __restrict__ Wbuf, const double* __restrict__ Ubuf,
+                              const double* __restrict__ bmat, const double* __restrict__ aux,
+                              const int32_t* __restrict__ perm, double* __restrict__ sample_ll,
+                              double* __restrict__ ll_no_dla, int k, int nseg) {
+  extern __shared__ __align__(128) unsigned char k2_smem_raw[];
+  double* smem = reinterpret_cast<double*>(k2_smem_raw);
+  double* Cs = smem + (size_t)K2P_STAGES * K2P_STAGE_DOUBLES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(Cs + K2P_C_DOUBLES);
+  uint64_t* empty = full + K2P_STAGES;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int s = 0; s < K2P_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], K2P_CONSUMER_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp >= K2P_CONSUMER_WARPS) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    if (warp == K2P_CONSUMER_WARPS && lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int ql = t / nsb, sb = t - ql * nsb;
+        const QuasarDesc* dp = desc + q0 + ql;
+        const int npad = dp->npad;
+        const int64_t wu_off = dp->wu_off + (int64_t)sb * (npad >> 2) * (TS * 4);
+        const double* Wsrc = Wbuf + wu_off;
+        const double* Usrc = Ubuf + wu_off;
+        const double* Bsrc = bmat + dp->bmat_off;
+        const int nchunks = npad / K2P_KC;
+        for (int c = 0; c < nchunks; ++c, ++it) {
+          const int st = it % K2P_STAGES;
+          mbar_wait(&empty[st], ((it / K2P_STAGES) & 1) ^ 1);
+          double* dst = smem + (size_t)st * K2P_STAGE_DOUBLES;
+          mbar_expect_tx(&full[st], K2P_STAGE_DOUBLES * 8);
+          bulk_g2s(dst, Wsrc + (int64_t)c * K2P_W_DOUBLES, K2P_W_DOUBLES * 8, &full[st]);
+          bulk_g2s(dst + K2P_W_DOUBLES, Usrc + (int64_t)c * K2P_W_DOUBLES, K2P_W_DOUBLES * 8, &full[st]);
+          bulk_g2s(dst + 2 * K2P_W_DOUBLES, Bsrc + (int64_t)c * K2P_B_DOUBLES, K2P_B_DOUBLES * 8, &full[st]);
+        }
+      }
+    }
+    return;
+  }
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+  uint32_t it = 0;
+  double* Cw = Cs + (size_t)(8 * warp) * LDC;   // this warp's eight C rows
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int ql = t / nsb, sb = t - ql * nsb;
+    const int n = desc[q0 + ql].n;
+    const int nchunks = desc[q0 + ql].npad / K2P_KC;
+    double acc[NT][2];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) acc[j][0] = acc[j][1] = 0.0;
+    for (int c = 0; c < nchunks; ++c, ++it) {
+      const int st = it % K2P_STAGES;
+      mbar_wait(&full[st], (it / K2P_STAGES) & 1);
+      const double* Ws = smem + (size_t)st * K2P_STAGE_DOUBLES;
+      const double* Us = Ws + K2P_W_DOUBLES;
+      const double* Bs = Us + K2P_W_DOUBLES;
+#pragma unroll
+      for (int kc = 0; kc < K2P_KC / 4; ++kc) {
+        const double aw = Ws[kc * (TS * 4) + warp * 32 + lane];
+        const double au = Us[kc * (TS * 4) + warp * 32 + lane];
+        const double* bp = Bs + kc * (NCOL * 4) + lane;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) dmma884(acc[j][0], acc[j][1], j >= PHI_TILES ? au : aw, bp[j * 32]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[st]);
+    }
+    {
+      double* p0 = Cw + (size_t)(lane >> 2) * LDC + 2 * (lane & 3);
+#pragma unroll
+      for (int j = 0; j < NT; ++j) { p0[j * 8] = acc[j][0]; p0[j * 8 + 1] = acc[j][1]; }
+    }
+    __syncwarp();
+    {
+      const int srow = 8 * warp + (lane >> 2), q4 = lane & 3;
+      const int64_t s = (int64_t)sb * TS + srow;
+      const int64_t S_pad = (int64_t)nsb * TS;
+      double q0v, ldv;
+      aux_sums(aux, ql, nseg, S_pad, s, q0v, ldv);
+      const double lp = chol_logp_quad<2>(Cs + (size_t)srow * LDC, k, q4, q0v, ldv, n);
       if (q4 == 0) {
         if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
         else if (s == S) ll_no_dla[q0 + ql] = lp;
@@ -1583,7 +1688,7 @@ fused_voigt_contract_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb
       const double* a0 = auxs + (((tcount & 1) * 2 + 0) * TS + srow) * 2;
       const double* a1 = auxs + (((tcount & 1) * 2 + 1) * TS + srow) * 2;
       const double q0v = a0[0] + a1[0], ldv = a0[1] + a1[1];
-      const double lp = chol_logp_quad<true>(Cs + (size_t)srow * LDC, k, q4, q0v, ldv, n);
+      const double lp = chol_logp_quad<1>(Cs + (size_t)srow * LDC, k, q4, q0v, ldv, n);
       if (q4 == 0) {
         if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
         else if (s == S) ll_no_dla[q0 + ql] = lp;

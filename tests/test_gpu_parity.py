@@ -298,3 +298,14 @@ def test_config4_dense_sampling_properties():
     sub = _run_gpu(prepared, Sub, 20, 10000, sp.log_priors_dla, sp.log_priors_no_dla)
     rel = np.abs(sub["sample_log_likelihoods_dla"] - ll[:, :10000]) / np.abs(ll[:, :10000])
     assert rel.max() <= 1e-10
+
+
+def test_config1_full_sample_set_parity(oracle):
+    """BASELINE config 1 at its full num_dla_samples = 10000 on six quasars (the C oracle with voigt.c verbatim
+    takes ~0.5 s per quasar on 16 host threads): every north_star gate at the real size."""
+    params, model, samples, sp, prepared = prepared_config("config1", 6, 10000)
+    got = _run_gpu(prepared, samples, 20, 10000, sp.log_priors_dla, sp.log_priors_no_dla)
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    worst = assert_parity(got, ref)
+    print("config1 full-S worst per-sample rel err", worst,
+          "log-posterior abs err", np.max(np.abs(got["log_posteriors_dla"] - ref["log_posteriors_dla"])))
