@@ -815,7 +815,7 @@ voigt_weights_lane_gather_kernel(const QuasarDesc* __restrict__ desc, int q0, in
   const int ql = tile / nsb, sb = tile % nsb;
   const QuasarDesc d = desc[q0 + ql];
   const int tid = threadIdx.x;
-  const int n_full = d.P - 6, n = d.n, npad = d.npad, npc = npad >> 2;
+  const int n_full = d.P - 6, npad = d.npad, npc = npad >> 2;
   const int ngrp = (n_full + 3) >> 2;                         // groups of 4 profile positions
   const int g0 = (int)(((int64_t)seg * ngrp) / nseg), g1 = (int)(((int64_t)(seg + 1) * ngrp) / nseg);
   const int i0 = 4 * g0, i1 = min(4 * g1, n_full);            // profile positions of this segment
