@@ -309,3 +309,19 @@ def test_config1_full_sample_set_parity(oracle):
     worst = assert_parity(got, ref)
     print("config1 full-S worst per-sample rel err", worst,
           "log-posterior abs err", np.max(np.abs(got["log_posteriors_dla"] - ref["log_posteriors_dla"])))
+
+
+def test_threaded_multi_context_sharding_matches_single_context():
+    """process_qsos_multi_gpu: one host thread and one dla_ctx per shard (here all on cuda:0, or on two GPUs when
+    the box has them); results are bitwise those of a single context, in batch order."""
+    import torch
+    from gp_dla_detection_b200.sharding import process_qsos_multi_gpu
+    params, model, samples, sp, prepared = prepared_config("config3", 7, 128)
+    args = (sp.all_wavelengths, sp.all_flux, sp.all_noise_variance, sp.all_pixel_mask, sp.z_qsos, model, samples,
+            sp.log_priors_dla, sp.log_priors_no_dla, params)
+    one = process_qsos(*args, device_prep=True)
+    devs = (0, 1, 0) if torch.cuda.device_count() > 1 else (0, 0, 0)
+    many = process_qsos_multi_gpu(*args, devices=devs)
+    for key in ("sample_log_likelihoods_dla", "log_likelihoods_dla", "log_likelihoods_no_dla", "model_posteriors",
+                "map_ind", "min_z_dlas", "max_z_dlas", "p_dlas", "map_z_dlas"):
+        assert np.array_equal(one[key], many[key], equal_nan=True), key
