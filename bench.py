@@ -28,9 +28,9 @@ sys.path.insert(0, ROOT)
 
 METRIC = "quasars/sec"
 N_PIX, K_RANK = 1217, 20
-# K2's DRAM traffic per quasar from the committed ncu --set full capture (1.6245 + 0.0045 GB for one
-# 8-quasar launch, profiles/r01_ncu_full_summary.txt); not measured inside bench.py
-NCU_K2_DRAM_GB_PER_QUASAR = (1.624543 + 0.004485) / 8
+# K2's DRAM traffic per quasar from the committed ncu --set full capture (3.2578 GB read + 0.0061 GB written
+# by one 16-quasar launch, profiles/r01_ncu_full_summary.txt); not measured inside bench.py
+NCU_K2_DRAM_GB_PER_QUASAR = (3.257835 + 0.006098) / 16
 # BASELINE.json configs as (rank, grid spacing, ragged masking, hypotheses); SURVEY.md 8(d)
 WORKLOADS = {
     "config2": {"k": 20, "dlambda": 0.25, "ragged": False, "samples": 10000, "pixels": 1217,
@@ -361,7 +361,7 @@ def run_ours(args):
                 "achieved": ach, "peak": dgemm_tflops, "unit": "TFLOP/s", "frac": ach / dgemm_tflops,
                 "traffic": (NCU_K2_DRAM_GB_PER_QUASAR * Q / max(1, tm["chunks"])) if args.workload == "config2" and S == 10000 else None,
                 "traffic_unit": "GB per launch (dram__bytes_read.sum + dram__bytes_write.sum of profiles/r01_ncu_full_summary.txt, "
-                                "scaled from its 8-quasar launch; algorithmic W+U bytes are 0.198 GB per quasar)",
+                                "scaled from its 16-quasar launch; algorithmic W+U bytes are 0.198 GB per quasar)",
                 "peak_source": "FP64 tensor peak = cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json "
                                "has no FP64 figure; the profiling guide states no FP64 fallback)",
                 "algorithmic_flop_per_launch": flop_per_step / max(1, tm["chunks"]),

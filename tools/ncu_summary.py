@@ -24,7 +24,7 @@ rows = list(csv.reader(io.StringIO(raw)))
 hdr, units = rows[0], rows[1]
 with open(f"profiles/{tag}_ncu_full_summary.txt", "w") as f:
     f.write("ncu --set full --clock-control none, bench.py --steps 1 --warmup 1 --quasars 16 --no-cpu-baseline\n"
-            "(per launch: one chunk of 8 quasars x 10000 hypotheses, 1217 px, k=20; profiler-serialised, cold cache)\n\n")
+            "(per launch: one chunk of 16 quasars x 10000 hypotheses, 1217 px, k=20; profiler-serialised, cold cache)\n\n")
     for r in rows[2:]:
         d = dict(zip(hdr, r))
         f.write(f"== {d['Kernel Name'][:60]}\n")
