@@ -521,18 +521,19 @@ constexpr int K1S_THREADS = TS;  // one CTA = 64 hypotheses x ONE spectrum segme
 // exp(t), t <= 0, result >= 2^-1020 (t is clamped at -707: a transmission of 1e-307 and one of 0
 // are the same number to every consumer: a^2 underflows either way).  NaN propagates.
 __device__ __forceinline__ double exp_tab256(double t, const double* __restrict__ etab_s) {
-  // clamp on the high word (t <= 0 here; a positive NaN compares below the threshold and propagates)
-  if ((unsigned)__double2hiint(t) > 0xC0861800u) t = -707.0;  // hi word of -707.0
+  // clamp on the high word alone (t <= 0 here, so a larger unsigned high word is a more negative t; the low
+  // word stays: t lands in [-707.001, -707]); a positive NaN compares below the threshold and propagates
+  t = __hiloint2double((int)min((unsigned)__double2hiint(t), 0xC0861800u), __double2loint(t));  // hi word of -707.0
   const double kd = fma(t, g_lines.k256, g_lines.magic);
   const int ki = __double2loint(kd);
   const double kf = kd - g_lines.magic;
   const double r = fma(kf, g_lines.nln2_256, t);
-  double p = fma(r, 1.0 / 24.0, 1.0 / 6.0);
+  double p = fma(r, g_lines.ec[4], g_lines.ec[3]);  // constant-bank operands (no immediate moves)
   p = fma(p, r, 0.5);
   p = fma(p, r, 1.0);
   p = fma(p, r, 1.0);
   const double tv = etab_s[ki & 255];  // 2^(i/256) in [1, 2): adding m to its exponent field stays normal
-  const double sc = __hiloint2double(__double2hiint(tv) + ((ki >> 8) << 20), __double2loint(tv));
+  const double sc = __hiloint2double((ki >> 8) * 0x100000 + __double2hiint(tv), __double2loint(tv));  // one shift + one IMAD
   return p * sc;
 }
 
@@ -571,8 +572,8 @@ __device__ __forceinline__ double wing_7(double sp, int j, double ncw, double to
 // redone with the reference's rounding (warp-uniform branch, rare).
 template <int NPIX>
 __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const double (&mult)[3],
-                                         const double (&ncw)[3], double N, const double* etab_s,
-                                         double (&out)[NPIX]) {
+                                         const double (&ncw)[3], const double (&nc1)[3], const double (&nc2)[3],
+                                         double N, const double* etab_s, double (&out)[NPIX]) {
   double sp[NPIX][3];
   int minhi = 0x7fffffff;
   const double negc = -g_lines.c_cgs;
@@ -597,10 +598,12 @@ __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const dou
 #pragma unroll
   for (int p = 0; p < NPIX; ++p) total[p] = 0.0;
   if (wmin >= g_lines.hi_256) {
+    // three-term series with the per-lane factors folded in: sp (ncw + sp (c1 + sp c2))
 #pragma unroll
     for (int j = 0; j < 3; ++j)
 #pragma unroll
-      for (int p = 0; p < NPIX; ++p) total[p] = wing_far<3>(sp[p][j], j, ncw[j], total[p]);
+      for (int p = 0; p < NPIX; ++p)
+        total[p] = fma(sp[p][j], fma(sp[p][j], fma(sp[p][j], nc2[j], nc1[j]), ncw[j]), total[p]);
   } else if (wmin >= g_lines.hi_64x) {
 #pragma unroll
     for (int j = 0; j < 3; ++j)
@@ -639,8 +642,11 @@ template <bool TAIL>
 __device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int n, int jdead, const double2* px /* shared */,
                                              double* __restrict__ wp, double* __restrict__ up, double& q0acc,
                                              double& ldacc, double& dprod, int& esum) {
+  // d within 2^+-200 (integer compares on the high word): the product of four such factors and a value in
+  // [1,2) cannot leave the normal range
+  constexpr unsigned LO = (1023 - 200) << 20, SPAN = 400u << 20;
   double w[4], u[4], dd[4];
-  bool allok = true;
+  unsigned hmin = 0xffffffffu, hmax = 0u;
 #pragma unroll
   for (int h = 0; h < 4; ++h) {
     const int j = 4 * g + h;
@@ -648,23 +654,20 @@ __device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int
     const int jc = live ? j : jdead;
     const double2 p01 = px[2 * jc];      // {omega2, noise}
     const double2 p23 = px[2 * jc + 1];  // {mu, flux}
-    double a = 0.0;  // voigt.c:297-299: zero-initialised, accumulated in tap order
+    // voigt.c:297-299: zero-initialised, accumulated in tap order (0 + x y rounds like x y)
+    double a = win[h] * dla_instrument_profile[0];
 #pragma unroll
-    for (int t = 0; t < 7; ++t) a = fma(win[h + t], dla_instrument_profile[t], a);
+    for (int t = 1; t < 7; ++t) a = fma(win[h + t], dla_instrument_profile[t], a);
     const double a2 = a * a;
     const double d_ = fma(p01.x, a2, p01.y);     // process_qsos.m:193, :197
     const double r = fma(-p23.x, a, p23.y);      // process_qsos.m:191, log_mvnpdf_low_rank.m:11
     const double rinv = rcp_cubic(d_);           // log_mvnpdf_low_rank.m:13
     const double gq_ = a * rinv;
     const double wv = a * gq_, uv = r * gq_, rr = r * rinv;
-    // d within 2^+-200 (one integer compare on the high word): the running product of four such
-    // factors and a value in [1,2) cannot leave the normal range
-    bool ok = (unsigned)(__double2hiint(d_) - ((1023 - 200) << 20)) < (unsigned)(400 << 20);
     if (TAIL) {
       w[h] = live ? wv : 0.0;
       u[h] = live ? uv : 0.0;
       q0acc = live ? fma(r, rr, q0acc) : q0acc;
-      ok = ok || !live;
       dd[h] = live ? d_ : 1.0;
     } else {
       w[h] = wv;
@@ -672,13 +675,24 @@ __device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int
       q0acc = fma(r, rr, q0acc);
       dd[h] = d_;
     }
-    allok = allok && ok;
-    dprod *= ok ? dd[h] : 1.0;
+    const unsigned hw = (unsigned)__double2hiint(dd[h]);
+    hmin = min(hmin, hw);
+    hmax = max(hmax, hw);
   }
-  if (!allok) {  // rare: zero / denormal / huge / NaN d -> exact log
+  if (hmin - LO < SPAN && hmax - LO < SPAN) {
+    dprod *= (dd[0] * dd[1]) * (dd[2] * dd[3]);
+  } else {  // rare: zero / denormal / huge / negative / NaN d -> exact log of that factor
 #pragma unroll
-    for (int h = 0; h < 4; ++h)
-      if (!((unsigned)(__double2hiint(dd[h]) - ((1023 - 200) << 20)) < (unsigned)(400 << 20))) ldacc += log(dd[h]);
+    for (int h = 0; h < 4; ++h) {
+      if ((unsigned)__double2hiint(dd[h]) - LO < SPAN) {
+        dprod *= dd[h];
+        const int hi = __double2hiint(dprod), e = (hi >> 20) - 1023;
+        esum += e;
+        dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
+      } else {
+        ldacc += log(dd[h]);
+      }
+    }
   }
   {
     const int hi = __double2hiint(dprod);
@@ -714,12 +728,15 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
   const int g0 = (int)(((int64_t)seg * npc) / nseg), g1 = (int)(((int64_t)(seg + 1) * npc) / nseg);
   const int lbase = max(4 * g0 - 2, 0), llast = min(4 * g1 + 5, Pm1);  // wavelengths this segment touches
   const int j0 = 4 * g0, j1 = min(4 * g1, n);                          // kept pixels this segment emits
+  const int nsteps = g1 - g0 + 2;
   double* lam_s = k1s_smem;
   double2* px_s = reinterpret_cast<double2*>(k1s_smem + lam_cap);
   for (int i = tid; i < 256; i += K1S_THREADS) etab_s[i] = etab256[i];
   {
-    const double* lam_g = padded_wavelengths + d.pad_off + lbase;
-    for (int i = tid; i <= llast - lbase; i += K1S_THREADS) lam_s[i] = __ldg(lam_g + i);
+    // lam_s[i] = wavelength at padded position 4 g0 - 2 + i, clamped to the segment's range: step st reads
+    // lam_s[4 st .. 4 st + 3] with two aligned 16-byte loads and no index arithmetic
+    const double* lam_g = padded_wavelengths + d.pad_off;
+    for (int i = tid; i < 4 * nsteps; i += K1S_THREADS) lam_s[i] = __ldg(lam_g + min(max(4 * g0 - 2 + i, lbase), llast));
     const double2* px_g = pix4 + 2 * (d.pix_off + j0);
     for (int i = tid; i < 2 * (j1 - j0); i += K1S_THREADS) px_s[i] = __ldg(px_g + i);
   }
@@ -732,13 +749,14 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
   const double N = real ? nhi_sorted[s] : 0.0;
   const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), off));
   const double opz = __dadd_rn(1.0, z);
-  double mult[3], ncw[3];
+  double mult[3], ncw[3], nc1[3], nc2[3];
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
     mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;  // voigt.c:278-279
     ncw[j] = -N * g_lines.cwT[j];
+    nc1[j] = ncw[j] * g_lines.g1p[j];
+    nc2[j] = ncw[j] * g_lines.gq[2];
   }
-  const double* lam = lam_s - lbase;            // indexed by the padded-grid position
   const double2* px = px_s - 2 * j0;            // indexed by 2 * kept pixel
   const int gfull = n >> 2;  // groups [0, gfull) have four live pixels
   const int64_t S_pad = (int64_t)nsb * TS;
@@ -752,13 +770,13 @@ voigt_weights_lane_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, 
   for (int t = 0; t < 10; ++t) win[t] = 0.0;
   // step st computes raw[b .. b+3], b = 4 (g0 + st) - 2, and (from st = 2 on) emits group g0 + st - 2,
   // whose window raw[4g .. 4g+9] is then complete
-  const int nsteps = g1 - g0 + 2;
   for (int st = 0; st < nsteps; ++st) {
-    const int b = 4 * (g0 + st) - 2;
     double l4[4], r4[4];
-#pragma unroll
-    for (int h = 0; h < 4; ++h) l4[h] = lam[min(max(b + h, lbase), llast)];
-    raw_lane<4>(l4, mult, ncw, N, etab_s, r4);
+    {
+      const double2 la = reinterpret_cast<const double2*>(lam_s)[2 * st], lb = reinterpret_cast<const double2*>(lam_s)[2 * st + 1];
+      l4[0] = la.x, l4[1] = la.y, l4[2] = lb.x, l4[3] = lb.y;
+    }
+    raw_lane<4>(l4, mult, ncw, nc1, nc2, N, etab_s, r4);
 #pragma unroll
     for (int t = 0; t < 6; ++t) win[t] = win[t + 4];
 #pragma unroll
@@ -842,11 +860,13 @@ voigt_weights_lane_gather_kernel(const QuasarDesc* __restrict__ desc, int q0, in
   const double N = real ? nhi_sorted[s] : 0.0;
   const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), off));
   const double opz = __dadd_rn(1.0, z);
-  double mult[3], ncw[3];
+  double mult[3], ncw[3], nc1[3], nc2[3];
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
     mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;
     ncw[j] = -N * g_lines.cwT[j];
+    nc1[j] = ncw[j] * g_lines.g1p[j];
+    nc2[j] = ncw[j] * g_lines.gq[2];
   }
   const double* lam = lam_s - lbase;
   const double2* px = px_s - 2 * k0;
@@ -890,7 +910,7 @@ voigt_weights_lane_gather_kernel(const QuasarDesc* __restrict__ desc, int q0, in
     double l4[4], r4[4];
 #pragma unroll
     for (int h = 0; h < 4; ++h) l4[h] = lam[min(max(b + h, lbase), llast)];
-    raw_lane<4>(l4, mult, ncw, N, etab_s, r4);
+    raw_lane<4>(l4, mult, ncw, nc1, nc2, N, etab_s, r4);
 #pragma unroll
     for (int t = 0; t < 6; ++t) win[t] = win[t + 4];
 #pragma unroll
@@ -1568,11 +1588,13 @@ fused_voigt_contract_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb
       const double N = real ? nhi_sorted[s] : 0.0;
       const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), off));  // process_qsos.m:163-165
       const double opz = __dadd_rn(1.0, z);
-      double mult[3], ncw[3];
+      double mult[3], ncw[3], nc1[3], nc2[3];
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
         mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;  // voigt.c:278-279
         ncw[j] = -N * g_lines.cwT[j];
+        nc1[j] = ncw[j] * g_lines.g1p[j];
+        nc2[j] = ncw[j] * g_lines.gq[2];
       }
       const double* lam = padded_wavelengths + d.pad_off;
       const double2* px = pix4 + 2 * d.pix_off;
@@ -1587,7 +1609,7 @@ fused_voigt_contract_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb
         double l4[4], r4[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) l4[u] = __ldg(lam + min(r0 + u, Pm1));
-        raw_lane<4>(l4, mult, ncw, N, etab_s, r4);
+        raw_lane<4>(l4, mult, ncw, nc1, nc2, N, etab_s, r4);
 #pragma unroll
         for (int u = 0; u < 4; ++u) ring[((r0 + u) & (KF_RING - 1)) * TS + h] = r4[u];
       };
