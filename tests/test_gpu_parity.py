@@ -325,3 +325,19 @@ def test_threaded_multi_context_sharding_matches_single_context():
     for key in ("sample_log_likelihoods_dla", "log_likelihoods_dla", "log_likelihoods_no_dla", "model_posteriors",
                 "map_ind", "min_z_dlas", "max_z_dlas", "p_dlas", "map_z_dlas"):
         assert np.array_equal(one[key], many[key], equal_nan=True), key
+
+
+@pytest.mark.parametrize("cfg,Q,S,k", [("config1", 100, 10000, 20), ("config3", 64, 2000, 20),
+                                        ("config4", 2, 100000, 20), ("config5", 8, 1000, 40)])
+def test_survey_parity_subsamples(oracle, cfg, Q, S, k):
+    """parity on ALL of config 1 (100 quasars x 10000 hypotheses) and on seeded subsamples of the
+    other configs, every north_star gate, against the C oracle (voigt.c verbatim when oracle/_ref is built; the
+    oracle runs on all host threads, about a minute in total)."""
+    params, model, samples, sp, prepared = prepared_config(cfg, Q, S)
+    got = _run_gpu(prepared, samples, k, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    worst = assert_parity(got, ref)
+    dec = got["log_posteriors_dla"] > got["log_posteriors_no_dla"]
+    print(f"{cfg}: {Q} quasars x {S}: worst per-sample rel err {worst:.2e}, log-posterior abs err "
+          f"{np.max(np.abs(got['log_posteriors_dla'] - ref['log_posteriors_dla'])):.2e}, "
+          f"{int(dec.sum())} DLA decisions (all equal to the oracle's)")
