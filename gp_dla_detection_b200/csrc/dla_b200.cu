@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "kernels.cuh"
@@ -103,10 +104,19 @@ struct dla_ctx {
   int64_t n_rest = 0;
   dla_prep_params prep{};
   DevBuf d_mrest, d_mmu, d_mM, d_mlo, d_lamk, d_zq;
-  PinBuf h_lamk, h_fk, h_nk, h_padded, h_pidx;
+  // dla_eval_spectra's compacted arrays of one sub-batch of quasars (page-locked: async H2D); two sets, so that a
+  // host thread can select the next sub-batch while the device works on the current one
+  struct SpectraStage {
+    PinBuf lamk, fk, nk, padded, pidx;
+    std::vector<int64_t> pix_ptr, pad_ptr;
+    std::vector<double> minz, maxz;
+    int64_t nkept = 0;
+    int rc = 0;
+    const char* err = nullptr;
+  } sstage[2];
   // training objective (dla_train_set_data / dla_train_objective)
   int64_t tQ = 0, tN = 0;
-  DevBuf t_y, t_l, t_nv, t_x, t_om2, t_aux, t_E, t_fq, t_beta, t_P, t_A1, t_S, t_gp, t_g, t_gsc, t_desc;  // dla_eval_spectra's compacted arrays (page-locked: async H2D)
+  DevBuf t_y, t_l, t_nv, t_x, t_om2, t_aux, t_E, t_fq, t_beta, t_P, t_A1, t_S, t_gp, t_g, t_gsc, t_desc;
   // hypothesis set
   // (sorted by offset once: the hypotheses of a warp are then neighbours in z; d_perm maps a
   //  sorted position back to the caller's sample index)
@@ -507,7 +517,8 @@ void dla_destroy(dla_ctx* c) {
     b->release();
   for (auto& ev : c->ev)
     if (ev) cudaEventDestroy(ev);
-  for (PinBuf* b : {&c->h_lamk, &c->h_fk, &c->h_nk, &c->h_padded, &c->h_pidx}) b->release();
+  for (auto& st : c->sstage)
+    for (PinBuf* b : {&st.lamk, &st.fk, &st.nk, &st.padded, &st.pidx}) b->release();
   for (auto& ev : c->ev_time) cudaEventDestroy(ev);
   for (auto& ev : c->ev_sync) cudaEventDestroy(ev);
   if (c->s_in) cudaStreamDestroy(c->s_in);
@@ -603,6 +614,23 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
     const int64_t pipe = std::min<int64_t>(max_pipe_chunks, Q / 8);
     const int64_t nch = std::max<int64_t>(std::max<int64_t>(1, pipe), (int64_t)ceill(total / budget));
     const long double target = total / nch;
+    // quasar-count cap of a chunk: the persistent contraction runs nq * nsb tiles in waves of num_sms; among the
+    // counts within 1/8 below what the budget allows, take the one whose last wave is fullest (up to 1 % of K2)
+    int64_t nq_cap = INT32_MAX;
+    if (Q > 0) {
+      long double max_bts = 0;
+      for (int64_t q = 0; q < Q; ++q) max_bts = std::max(max_bts, 16.0L * S_pad * c->h_desc[(size_t)q].npad + gq);
+      const int64_t nq_budget = std::max<int64_t>(1, (int64_t)(budget / max_bts));
+      if (nq_budget >= 8 && nq_budget < Q) {
+        const int64_t nsb = S_pad / dla::TS;
+        double best = -1.0;
+        for (int64_t cand = nq_budget; cand >= nq_budget - nq_budget / 8; --cand) {
+          const int64_t tiles = cand * nsb, waves = (tiles + c->num_sms - 1) / c->num_sms;
+          const double eff = (double)tiles / (double)(waves * c->num_sms);
+          if (eff > best + 1e-9) { best = eff; nq_cap = cand; }
+        }
+      }
+    }
     int64_t q = 0;
     while (q < Q) {
       Chunk ch{(int)q, 0, 0, 0, 0, 0, true};
@@ -610,7 +638,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
       while (q < Q) {
         QuasarDesc& d = c->h_desc[(size_t)q];
         const long double bts = 16.0L * S_pad * d.npad + gq;
-        if (ch.nq > 0 && (acc + bts > budget || acc >= target)) break;
+        if (ch.nq > 0 && (acc + bts > budget || acc >= target || ch.nq >= nq_cap)) break;
         d.wu_off = ch.wu_doubles;
         d.bmat_off = ch.bmat_doubles;
         ch.wu_doubles += S_pad * d.npad;
@@ -893,41 +921,26 @@ int dla_set_model(dla_ctx* c, int64_t n_rest, const double* rest_wavelengths, co
   return DLA_OK;
 }
 
-int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const double* wavelengths, const double* flux,
-                     const double* noise_variance, const uint8_t* pixel_mask, const double* z_qso,
-                     const double* log_prior_dla, const double* log_prior_no_dla, int32_t mask_gather,
-                     double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
-                     double* log_post_dla, double* model_posteriors, int32_t* map_index, double* min_z_out,
-                     double* max_z_out) {
-  if (!c) return DLA_ERR_BAD_ARG;
-  if (!c->have_model) {
-    c->err = "dla_eval_spectra: dla_set_model has not been called";
-    return DLA_ERR_STATE;
-  }
-  if (Q < 0 || !spec_ptr || !wavelengths || !flux || !noise_variance || !pixel_mask || !z_qso || !log_prior_dla ||
-      !log_prior_no_dla)
-    BAD_ARG(c, "dla_eval_spectra: NULL pointer");
-  if (mask_gather != 0 && mask_gather != 1) BAD_ARG(c, "dla_eval_spectra: mask_gather must be 0 or 1");
-  if (sample_ll && !c->p.store_sample_ll) BAD_ARG(c, "dla_eval_spectra: sample_ll requested but store_sample_ll = 0");
-  const dla_prep_params& pp = c->prep;
-  // one host pass per quasar: process_qsos.m:102-116 (selection), :160-161 (z range), :169-180 (padded grid, gather)
-  std::vector<int64_t> pix_ptr((size_t)Q + 1, 0), pad_ptr((size_t)Q + 1, 0);
-  std::vector<double> minz((size_t)Q), maxz((size_t)Q);
-  const int64_t ntot = spec_ptr[Q] - spec_ptr[0];
-  if (ntot < 0) BAD_ARG(c, "dla_eval_spectra: spec_ptr must be non-decreasing");
-  CU_TRY(c, cudaSetDevice(c->device));
-  CU_TRY(c, c->h_lamk.ensure((size_t)ntot * 8 + 64));
-  CU_TRY(c, c->h_fk.ensure((size_t)ntot * 8 + 64));
-  CU_TRY(c, c->h_nk.ensure((size_t)ntot * 8 + 64));
-  CU_TRY(c, c->h_pidx.ensure((size_t)ntot * 4 + 64));
-  CU_TRY(c, c->h_padded.ensure(((size_t)ntot + 6 * (size_t)Q) * 8 + 64));
-  double *lamk = c->h_lamk.as<double>(), *fk = c->h_fk.as<double>(), *nk = c->h_nk.as<double>();
-  double* padded = c->h_padded.as<double>();
-  int32_t* pidx = c->h_pidx.as<int32_t>();
+// One host pass over quasars [qa, qb): process_qsos.m:102-116 (selection), :160-161 (z range), :169-180 (padded
+// grid, gather).  Pure host code (no CUDA calls): runs on a helper thread for the NEXT sub-batch.
+static void select_spectra(const dla_prep_params pp, dla_ctx::SpectraStage* stp, int64_t qa, int64_t qb,
+                           const int64_t* spec_ptr, const double* wavelengths, const double* flux,
+                           const double* noise_variance, const uint8_t* pixel_mask, const double* z_qso,
+                           int32_t mask_gather) {
+  dla_ctx::SpectraStage& st = *stp;
+  const int64_t Qs = qb - qa;
+  st.rc = DLA_OK;
+  st.err = nullptr;
+  st.pix_ptr.assign((size_t)Qs + 1, 0);
+  st.pad_ptr.assign((size_t)Qs + 1, 0);
+  st.minz.assign((size_t)Qs, 0.0);
+  st.maxz.assign((size_t)Qs, 0.0);
+  double *lamk = st.lamk.as<double>(), *fk = st.fk.as<double>(), *nk = st.nk.as<double>();
+  double* padded = st.padded.as<double>();
+  int32_t* pidx = st.pidx.as<int32_t>();
   int64_t nkept = 0, npadded = 0;
-  for (int64_t q = 0; q < Q; ++q) {
+  for (int64_t q = qa; q < qb; ++q) {
     const int64_t a = spec_ptr[q], b = spec_ptr[q + 1];
-    if (b < a) BAD_ARG(c, "dla_eval_spectra: spec_ptr must be non-decreasing");
     const double opz = 1.0 + z_qso[q];
     const int64_t pad0 = npadded;
     npadded += 3;  // left pads, filled below
@@ -948,7 +961,11 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
       }
       ++n_full;
     }
-    if (n_full == 0 || n == 0) BAD_ARG(c, "dla_eval_spectra: a quasar has no unmasked pixel in the modelled range");
+    if (n_full == 0 || n == 0) {
+      st.rc = DLA_ERR_BAD_ARG;
+      st.err = "dla_eval_spectra: a quasar has no unmasked pixel in the modelled range";
+      return;
+    }
     // :169-177: width log-spaced pads each side, 10.^linspace(...)
     const double lo = log10(umin), hi = log10(umax), ps = pp.pixel_spacing;
     auto linspace3 = [](double x0, double x1, double* out) {  // numpy/MATLAB linspace(x0, x1, 3)
@@ -961,34 +978,108 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
     linspace3(hi + ps, hi + 3 * ps, e);
     for (int t = 0; t < 3; ++t) padded[npadded++] = pow(10.0, e[t]);
     // :160-161, set_parameters.m:66-73 (on the kept wavelengths)
-    maxz[(size_t)q] = (kmax / pp.lya_wavelength - 1) - pp.max_z_cut;
-    minz[(size_t)q] = std::max(kmin / pp.lya_wavelength - 1,
-                               pp.lyman_limit * (1 + z_qso[q]) / pp.lya_wavelength - 1 + pp.min_z_cut);
-    pix_ptr[(size_t)q + 1] = pix_ptr[(size_t)q] + n;
-    pad_ptr[(size_t)q + 1] = pad_ptr[(size_t)q] + n_full + 6;
+    const size_t ql = (size_t)(q - qa);
+    st.maxz[ql] = (kmax / pp.lya_wavelength - 1) - pp.max_z_cut;
+    st.minz[ql] = std::max(kmin / pp.lya_wavelength - 1,
+                           pp.lyman_limit * (1 + z_qso[q]) / pp.lya_wavelength - 1 + pp.min_z_cut);
+    st.pix_ptr[ql + 1] = st.pix_ptr[ql] + n;
+    st.pad_ptr[ql + 1] = st.pad_ptr[ql] + n_full + 6;
   }
-  c->dev_prep = true;
-  // mu / omega2 / M are produced on the device: any non-NULL pointer satisfies the planner
-  const double* dummy = fk;
-  int rc = plan_batch(c, Q, pix_ptr.data(), pad_ptr.data(), padded, pidx, fk, dummy, dummy, nk,
-                      dummy, minz.data(), maxz.data(), log_prior_dla, log_prior_no_dla, 4);
-  if (rc == DLA_OK) {
-    c->hin.lamk = lamk;
-    c->hin.zq = z_qso;
-    cudaError_t e1 = c->d_lamk.ensure(std::max<size_t>((size_t)nkept * 8, 32));
-    cudaError_t e2 = c->d_zq.ensure(std::max<size_t>((size_t)Q * 8, 32));
-    if (e1 != cudaSuccess || e2 != cudaSuccess) {
-      c->err = "dla_eval_spectra: device allocation failed";
-      rc = DLA_ERR_OOM;
+  st.nkept = nkept;
+}
+
+int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const double* wavelengths, const double* flux,
+                     const double* noise_variance, const uint8_t* pixel_mask, const double* z_qso,
+                     const double* log_prior_dla, const double* log_prior_no_dla, int32_t mask_gather,
+                     double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
+                     double* log_post_dla, double* model_posteriors, int32_t* map_index, double* min_z_out,
+                     double* max_z_out) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!c->have_model) {
+    c->err = "dla_eval_spectra: dla_set_model has not been called";
+    return DLA_ERR_STATE;
+  }
+  if (Q < 0 || !spec_ptr || !wavelengths || !flux || !noise_variance || !pixel_mask || !z_qso || !log_prior_dla ||
+      !log_prior_no_dla)
+    BAD_ARG(c, "dla_eval_spectra: NULL pointer");
+  if (mask_gather != 0 && mask_gather != 1) BAD_ARG(c, "dla_eval_spectra: mask_gather must be 0 or 1");
+  if (sample_ll && !c->p.store_sample_ll) BAD_ARG(c, "dla_eval_spectra: sample_ll requested but store_sample_ll = 0");
+  for (int64_t q = 0; q < Q; ++q)
+    if (spec_ptr[q + 1] < spec_ptr[q]) BAD_ARG(c, "dla_eval_spectra: spec_ptr must be non-decreasing");
+  CU_TRY(c, cudaSetDevice(c->device));
+  // Sub-batches of <= SUBQ quasars: the selection pass of sub-batch i+1 runs on a helper thread while the device
+  // evaluates sub-batch i, and the staging / device input buffers stay bounded however large Q is.
+  const int64_t SUBQ = 2048;
+  const int64_t nsub = std::max<int64_t>(1, (Q + SUBQ - 1) / SUBQ);
+  int64_t maxtot = 0, maxq = 0;
+  for (int64_t i = 0; i < nsub; ++i) {
+    const int64_t qa = i * SUBQ, qb = std::min(Q, qa + SUBQ);
+    maxtot = std::max(maxtot, spec_ptr[qb] - spec_ptr[qa]);
+    maxq = std::max(maxq, qb - qa);
+  }
+  for (int b = 0; b < (nsub > 1 ? 2 : 1); ++b) {
+    auto& st = c->sstage[b];
+    CU_TRY(c, st.lamk.ensure((size_t)maxtot * 8 + 64));
+    CU_TRY(c, st.fk.ensure((size_t)maxtot * 8 + 64));
+    CU_TRY(c, st.nk.ensure((size_t)maxtot * 8 + 64));
+    CU_TRY(c, st.pidx.ensure((size_t)maxtot * 4 + 64));
+    CU_TRY(c, st.padded.ensure(((size_t)maxtot + 6 * (size_t)maxq) * 8 + 64));
+  }
+  const dla_prep_params pp = c->prep;
+  select_spectra(pp, &c->sstage[0], 0, std::min(Q, SUBQ), spec_ptr, wavelengths, flux, noise_variance, pixel_mask,
+                 z_qso, mask_gather);
+  dla_timing acc{};
+  int rc = DLA_OK;
+  for (int64_t i = 0; i < nsub && rc == DLA_OK; ++i) {
+    const int64_t qa = i * SUBQ, qb = std::min(Q, qa + SUBQ), Qs = qb - qa;
+    auto& st = c->sstage[i & 1];
+    std::thread next;
+    if (i + 1 < nsub)
+      next = std::thread(select_spectra, pp, &c->sstage[(i + 1) & 1], qb, std::min(Q, qb + SUBQ), spec_ptr, wavelengths,
+                         flux, noise_variance, pixel_mask, z_qso, mask_gather);
+    if (st.rc != DLA_OK) {
+      c->err = st.err ? st.err : "dla_eval_spectra: selection failed";
+      rc = st.rc;
     }
+    if (rc == DLA_OK) {
+      c->dev_prep = true;
+      // mu / omega2 / M are produced on the device: any non-NULL pointer satisfies the planner
+      const double* fk = st.fk.as<double>();
+      const double* dummy = fk;
+      rc = plan_batch(c, Qs, st.pix_ptr.data(), st.pad_ptr.data(), st.padded.as<double>(), st.pidx.as<int32_t>(), fk,
+                      dummy, dummy, st.nk.as<double>(), dummy, st.minz.data(), st.maxz.data(), log_prior_dla + qa,
+                      log_prior_no_dla + qa, 4);
+      if (rc == DLA_OK) {
+        c->hin.lamk = st.lamk.as<double>();
+        c->hin.zq = z_qso + qa;
+        cudaError_t e1 = c->d_lamk.ensure(std::max<size_t>((size_t)st.nkept * 8, 32));
+        cudaError_t e2 = c->d_zq.ensure(std::max<size_t>((size_t)Qs * 8, 32));
+        if (e1 != cudaSuccess || e2 != cudaSuccess) {
+          c->err = "dla_eval_spectra: device allocation failed";
+          rc = DLA_ERR_OOM;
+        }
+      }
+      const int64_t S = c->p.num_samples;
+      if (rc == DLA_OK)
+        rc = run_pipelined(c, sample_ll ? sample_ll + qa * S : nullptr, ll_no_dla ? ll_no_dla + qa : nullptr,
+                           ll_dla ? ll_dla + qa : nullptr, log_post_no_dla ? log_post_no_dla + qa : nullptr,
+                           log_post_dla ? log_post_dla + qa : nullptr,
+                           model_posteriors ? model_posteriors + 2 * qa : nullptr, map_index ? map_index + qa : nullptr);
+      c->dev_prep = false;
+      c->staged = false;  // the staged-run API needs host-prepared inputs
+      if (rc == DLA_OK) {
+        if (min_z_out) memcpy(min_z_out + qa, st.minz.data(), (size_t)Qs * 8);
+        if (max_z_out) memcpy(max_z_out + qa, st.maxz.data(), (size_t)Qs * 8);
+        const dla_timing& t = c->timing;
+        acc.ms_phi += t.ms_phi; acc.ms_voigt += t.ms_voigt; acc.ms_contract += t.ms_contract;
+        acc.ms_reduce += t.ms_reduce; acc.ms_total += t.ms_total; acc.ms_h2d += t.ms_h2d; acc.ms_d2h += t.ms_d2h;
+        acc.h2d_bytes += t.h2d_bytes; acc.d2h_bytes += t.d2h_bytes; acc.chunks += t.chunks; acc.launches += t.launches;
+      }
+    }
+    if (next.joinable()) next.join();
   }
-  if (rc == DLA_OK)
-    rc = run_pipelined(c, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
-  c->dev_prep = false;
-  c->staged = false;  // the staged-run API needs host-prepared inputs
   if (rc != DLA_OK) return rc;
-  if (min_z_out) memcpy(min_z_out, minz.data(), (size_t)Q * 8);
-  if (max_z_out) memcpy(max_z_out, maxz.data(), (size_t)Q * 8);
+  c->timing = acc;
   return DLA_OK;
 }
 

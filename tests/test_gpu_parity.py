@@ -341,3 +341,38 @@ def test_survey_parity_subsamples(oracle, cfg, Q, S, k):
     print(f"{cfg}: {Q} quasars x {S}: worst per-sample rel err {worst:.2e}, log-posterior abs err "
           f"{np.max(np.abs(got['log_posteriors_dla'] - ref['log_posteriors_dla'])):.2e}, "
           f"{int(dec.sum())} DLA decisions (all equal to the oracle's)")
+
+
+def test_eval_spectra_sub_batches_are_seamless():
+    """dla_eval_spectra splits more than 2048 quasars into sub-batches (the host selection pass of one runs on a
+    helper thread under the device work of the previous one): one call over 2100 quasars == the same quasars
+    evaluated as [0, 2048) and [2048, 2100) in two calls, bit for bit, and == the host-prepared path."""
+    from gp_dla_detection_b200 import synthetic
+    from gp_dla_detection_b200.process_qsos import PackedSpectra
+    Q, S = 2100, 64
+    params, model, samples, sp = synthetic.make_config("tiny", num_quasars=Q, num_samples=S)
+    pack = lambda a, b: PackedSpectra(sp.all_wavelengths[a:b], sp.all_flux[a:b], sp.all_noise_variance[a:b],
+                                      sp.all_pixel_mask[a:b], sp.z_qsos[a:b])
+    with DlaContext(k=5, num_lines=3, num_samples=S) as ctx:
+        ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+        ctx.set_model(model, params)
+        whole = ctx.eval_spectra(pack(0, Q), sp.log_priors_dla, sp.log_priors_no_dla)
+        tm = ctx.timing()
+        first = ctx.eval_spectra(pack(0, 2048), sp.log_priors_dla[:2048], sp.log_priors_no_dla[:2048])
+        rest = ctx.eval_spectra(pack(2048, Q), sp.log_priors_dla[2048:], sp.log_priors_no_dla[2048:])
+    assert tm["chunks"] >= 2
+    for key in ("sample_log_likelihoods_dla", "log_likelihoods_dla", "log_likelihoods_no_dla", "log_posteriors_dla",
+                "model_posteriors", "map_ind", "min_z_dlas", "max_z_dlas"):
+        assert np.array_equal(whole[key], np.concatenate([first[key], rest[key]])), key
+    sel = [0, 1, 2047, 2048, 2099]
+    prepared = [prepare_quasar_(sp, q, model, params) for q in sel]
+    host = _run_gpu(prepared, samples, 5, S, sp.log_priors_dla[sel], sp.log_priors_no_dla[sel])
+    rel = np.abs(host["sample_log_likelihoods_dla"] - whole["sample_log_likelihoods_dla"][sel]) / \
+        np.abs(host["sample_log_likelihoods_dla"])
+    assert rel.max() <= 1e-10
+
+
+def prepare_quasar_(sp, q, model, params):
+    from gp_dla_detection_b200.process_qsos import prepare_quasar
+    return prepare_quasar(sp.all_wavelengths[q], sp.all_flux[q], sp.all_noise_variance[q], sp.all_pixel_mask[q],
+                          sp.z_qsos[q], model, params)
