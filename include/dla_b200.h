@@ -152,7 +152,11 @@ int dla_set_model(dla_ctx *ctx, int64_t n_rest, const double *rest_wavelengths, 
  * pixel_mask (1 = masked), z_qso [Q].  mask_gather: 0 = the gather as written in the
  * reference (process_qsos.m:180/:189: first n profile elements), 1 = the unmasked positions.
  * Outputs as dla_eval_batch, plus min_z_dla / max_z_dla [Q] (process_qsos.m:160-161; may be
- * NULL).  A quasar with no unmasked pixel in the modelled range is DLA_ERR_BAD_ARG. */
+ * NULL).  A quasar with no unmasked pixel in the modelled range is DLA_ERR_BAD_ARG.
+ * Q is unbounded: more than 2048 quasars are evaluated as consecutive sub-batches inside the
+ * call (one short-lived helper host thread selects the next sub-batch while the device works
+ * on the current one); the call is still synchronous, and on an error outputs of earlier
+ * sub-batches may already have been written. */
 int dla_eval_spectra(dla_ctx *ctx, int64_t Q, const int64_t *spec_ptr, const double *wavelengths,
                      const double *flux, const double *noise_variance, const uint8_t *pixel_mask,
                      const double *z_qso, const double *log_prior_dla, const double *log_prior_no_dla,
