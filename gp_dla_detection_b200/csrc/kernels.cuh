@@ -181,6 +181,10 @@ __device__ __forceinline__ double raw_transmission(double lambda, const double* 
 }
 
 __device__ __noinline__ double line_tau_slow(double lambda, double mult_j, int j) { return line_tau(lambda, mult_j, j); }
+// line core only (|x| < 16), x = |v| / (sqrt(2) sigma): lc_j V per unit column density (one out-of-line copy)
+__device__ __noinline__ double line_core_tau(double absx, int j) {
+  return g_lines.coef[j] * dla_re_w_near(absx, g_lines.y[j], dla_wgrid);
+}
 
 // One line's wing contribution with an NT-term series (NT = 7: |x| >= 16; 4: >= 64; 3: >= 256).
 // The O(y^3) correction keeps its (1 + 5 s) factor only where it matters (NT = 7).
@@ -610,26 +614,19 @@ __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const dou
 #pragma unroll
       for (int p = 0; p < NPIX; ++p) total[p] = wing_far<4>(sp[p][j], j, ncw[j], total[p]);
   } else {
-    // within ~64 widths of a line for some lane: the reference's velocity rounding, 7-term series,
-    // and the exact two-regime path for the lanes with a line core (|x| < 16) in these pixels
-    bool near = false;
+    // within ~64 widths of a line for some lane: the reference's velocity rounding and the 7-term series;
+    // a (pixel, line) pair inside a line core (|x| < 16) takes the table-based core evaluation instead --
+    // only that pair, and only on the lanes that need it (the other pairs of the step keep their series term)
 #pragma unroll
     for (int p = 0; p < NPIX; ++p) {
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
         const double velocity = __dsub_rn(__dmul_rn(lambda[p], mult[j]), g_lines.c_cgs);  // voigt.c:287
         const double v2e = velocity * velocity;
-        near = near || (__double2hiint(v2e) < g_lines.hi_near);
-        total[p] = wing_7(rcp_cubic(v2e), j, ncw[j], total[p]);
-      }
-    }
-    if (near) {
-#pragma unroll
-      for (int p = 0; p < NPIX; ++p) {
-        double t = 0.0;
-#pragma unroll
-        for (int j = 0; j < 3; ++j) t += line_tau_slow(lambda[p], mult[j], j);
-        total[p] = -N * t;
+        if (__double2hiint(v2e) < g_lines.hi_near)
+          total[p] = fma(-N, line_core_tau(fabs(velocity * g_lines.inv_sqrt2_sigma), j), total[p]);
+        else
+          total[p] = wing_7(rcp_cubic(v2e), j, ncw[j], total[p]);
       }
     }
   }
