@@ -376,3 +376,29 @@ def prepare_quasar_(sp, q, model, params):
     from gp_dla_detection_b200.process_qsos import prepare_quasar
     return prepare_quasar(sp.all_wavelengths[q], sp.all_flux[q], sp.all_noise_variance[q], sp.all_pixel_mask[q],
                           sp.z_qsos[q], model, params)
+
+
+def test_eval_spectra_error_in_a_later_sub_batch_is_reported():
+    """A quasar without any unmasked pixel in the modelled range is DLA_ERR_BAD_ARG (include/dla_b200.h) also when
+    it sits in the second sub-batch, i.e. when the helper thread found it while the first sub-batch was running;
+    the context stays usable afterwards.  Q = 0 is legal and returns empty arrays."""
+    from gp_dla_detection_b200 import _lib, synthetic
+    from gp_dla_detection_b200.process_qsos import PackedSpectra
+    Q, S = 2100, 64
+    params, model, samples, sp = synthetic.make_config("tiny", num_quasars=Q, num_samples=S)
+    masks = [m.copy() for m in sp.all_pixel_mask]
+    masks[2060][:] = True
+    with DlaContext(k=5, num_lines=3, num_samples=S) as ctx:
+        ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+        ctx.set_model(model, params)
+        bad = PackedSpectra(sp.all_wavelengths, sp.all_flux, sp.all_noise_variance, masks, sp.z_qsos)
+        with pytest.raises(_lib.DlaError) as ei:
+            ctx.eval_spectra(bad, sp.log_priors_dla, sp.log_priors_no_dla)
+        assert ei.value.status == -1 and "no unmasked pixel" in str(ei.value)
+        good = PackedSpectra(sp.all_wavelengths[:8], sp.all_flux[:8], sp.all_noise_variance[:8],
+                             sp.all_pixel_mask[:8], sp.z_qsos[:8])
+        out = ctx.eval_spectra(good, sp.log_priors_dla[:8], sp.log_priors_no_dla[:8])
+        assert np.all(np.isfinite(out["log_likelihoods_dla"]))
+        empty = PackedSpectra([], [], [], [], np.zeros(0))
+        out0 = ctx.eval_spectra(empty, np.zeros(0), np.zeros(0))
+        assert out0["log_likelihoods_dla"].shape == (0,)
