@@ -463,6 +463,12 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
       h.hi_64 = hi_of(64.0);
       h.hi_256 = hi_of(256.0);
       h.hi_64x = hi_of(64.5);
+      {  // high word of 1 / v^2 at 260 widths: a pair with hi(1/v^2) below it is safely beyond 256
+        const double v = 260.0 * sqrt(2.0) * sigma, r = 1.0 / (v * v);
+        long long bits;
+        memcpy(&bits, &r, 8);
+        h.hi_sp256 = (int)(bits >> 32);
+      }
     }
     CREATE_TRY(cudaMemcpyToSymbol(dla::g_lines, &h, sizeof h));
     double e256[256];

@@ -74,6 +74,7 @@ struct LineConsts {
   double k256, nln2hi256, nln2lo256;
   double nln2_256;             // -ln2/256 in one constant (|t| <= 707: reduction error <= 8e-14 at the far end)
   double g1p[DLA_MAX_LINES];   // gq[1] - y2T_j: the O(y^2) correction folded into the s^1 coefficient
+  int hi_sp256, pad_;          // high word of 1/v^2 at 260 widths (pair-wise series choice near a line)
 };
 __device__ __constant__ LineConsts g_lines;
 
@@ -621,6 +622,10 @@ __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const dou
     for (int p = 0; p < NPIX; ++p) {
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
+        if (__double2hiint(sp[p][j]) < g_lines.hi_sp256) {  // a far line (> 260 widths): its three-term series as above
+          total[p] = fma(sp[p][j], fma(sp[p][j], fma(sp[p][j], nc2[j], nc1[j]), ncw[j]), total[p]);
+          continue;
+        }
         const double velocity = __dsub_rn(__dmul_rn(lambda[p], mult[j]), g_lines.c_cgs);  // voigt.c:287
         const double v2e = velocity * velocity;
         if (__double2hiint(v2e) < g_lines.hi_near)
@@ -1080,8 +1085,9 @@ __device__ __forceinline__ double chol_logp_quad(const double* __restrict__ row,
       const double Llj = __shfl_sync(0xffffffffu, A[rl][j], tl, 4);
 #pragma unroll
       for (int r = rl; r < NR; ++r) {
-        const double m = (r > rl || t >= tl) ? A[r][j] : 0.0;  // only rows i >= l
-        A[r][l] = fma(-m, Llj, A[r][l]);
+        // rows i < l of column l (r == rl, t < tl) receive a meaningless update: entries above the diagonal are
+        // never read into an entry on or below it (every read is of (i, j) with i >= l > j), so no select
+        A[r][l] = fma(-A[r][j], Llj, A[r][l]);
       }
     }
   }
