@@ -166,3 +166,39 @@ def test_mex_shims_compile_and_link_against_the_c_abi(tmp_path):
         subprocess.run(["gcc", "-Wall", "-Werror", "-shared", "-fPIC", os.path.join(pkg, "mex", src), str(stub),
                         "-I", os.path.join(ROOT, "oracle", "shim"), "-I", os.path.join(ROOT, "include"),
                         "-L", pkg, "-l:libdla_b200.so", "-Wl,--no-undefined", "-o", str(out)], check=True, env=env)
+
+
+def test_threaded_multi_gpu_helper_merges_in_batch_order_and_reraises(monkeypatch):
+    """process_qsos_multi_gpu's host logic (LPT shards, one thread per device, merge back in batch order, worker
+    exceptions re-raised on the caller's thread) with the per-shard evaluation replaced by a stand-in: no GPU."""
+    import importlib
+    from gp_dla_detection_b200 import sharding
+    pq_mod = importlib.import_module("gp_dla_detection_b200.process_qsos")   # the package re-exports the function under this name
+    Q, S = 23, 7
+    rng = np.random.default_rng(1)
+    lens = rng.integers(50, 90, size=Q)
+    W = [np.full(n, float(i)) for i, n in enumerate(lens)]          # wavelengths[0] carries the quasar's identity
+    seen = {}
+
+    def fake_process_qsos(all_w, all_f, all_v, all_m, z, model, samples, lpd, lpn, params, device=0, **kw):
+        ids = np.array([int(w[0]) for w in all_w])
+        seen[device] = ids
+        if kw.get("store_sample_ll") is False and device == 1:
+            raise RuntimeError("boom on device 1")
+        return {"log_likelihoods_dla": ids * 2.0 + np.asarray(lpd), "map_ind": ids.astype(np.int32),
+                "sample_log_likelihoods_dla": np.outer(ids, np.ones(S)), "model_posteriors": np.tile(ids[:, None], (1, 2)) * 1.0,
+                "nothing": None}
+
+    monkeypatch.setattr(pq_mod, "process_qsos", fake_process_qsos)
+    z = np.linspace(2.2, 4.0, Q)
+    lpd = np.arange(Q) * 0.25
+    out = sharding.process_qsos_multi_gpu(W, W, W, W, z, None, None, lpd, -1.0, devices=(0, 1, 2))
+    assert np.array_equal(out["log_likelihoods_dla"], np.arange(Q) * 2.0 + lpd)
+    assert np.array_equal(out["map_ind"], np.arange(Q))
+    assert np.array_equal(out["sample_log_likelihoods_dla"][:, 3], np.arange(Q, dtype=float))
+    assert out["nothing"] is None
+    assert sorted(np.concatenate(list(seen.values())).tolist()) == list(range(Q)) and len(seen) == 3
+    loads = [lens[ids].sum() for ids in seen.values()]
+    assert max(loads) - min(loads) <= lens.max()                     # LPT balance by spectrum length
+    with pytest.raises(RuntimeError, match="boom on device 1"):
+        sharding.process_qsos_multi_gpu(W, W, W, W, z, None, None, lpd, -1.0, devices=(0, 1), store_sample_ll=False)
