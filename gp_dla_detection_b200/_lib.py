@@ -4,6 +4,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import threading
 
 import numpy as np
 
@@ -45,7 +46,8 @@ class dla_timing(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_phi", C.c_double), ("ms_voigt", C.c_double),
                 ("ms_contract", C.c_double), ("ms_reduce", C.c_double), ("ms_h2d", C.c_double),
                 ("ms_d2h", C.c_double), ("launches", C.c_int64), ("h2d_bytes", C.c_int64),
-                ("d2h_bytes", C.c_int64), ("chunks", C.c_int64)]
+                ("d2h_bytes", C.c_int64), ("chunks", C.c_int64), ("ms_chol", C.c_double),
+                ("contraction", C.c_int64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -60,6 +62,7 @@ _INPUTS = [_pi64, _pi64, _pd, _pi32, _pd, _pd, _pd, _pd, _pd, _pd, _pd, _pd, _pd
 _OUTPUTS = [_pd, _pd, _pd, _pd, _pd, _pd, _pi32]
 
 _lib = None
+_load_lock = threading.Lock()
 
 
 def load() -> C.CDLL:
@@ -67,9 +70,24 @@ def load() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        from . import build
-        build.build_library()
+    with _load_lock:
+        return _load_locked()
+
+
+def _load_locked() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    from . import build
+    if build.is_stale():
+        # missing, or older than a kernel source: rebuild when nvcc is here (the GPU box always has it); a stale
+        # binary without nvcc is an error, never a silent run of old kernels
+        try:
+            build.build_library()
+        except RuntimeError as e:
+            if os.path.exists(LIB_PATH) and "nvcc not found" in str(e):
+                raise ImportError(f"{LIB_PATH} is older than its sources and nvcc is not available to rebuild it") from e
+            raise
     if not os.path.exists(LIB_PATH):
         raise ImportError(f"{LIB_PATH} is missing: build it with `python -m gp_dla_detection_b200.build` "
                           "(nvcc, sm_100a). There is no CPU fallback.")

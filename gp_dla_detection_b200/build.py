@@ -14,7 +14,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libdla_b200.so")
 SOURCES = ["dla_b200.cu"]
-HEADERS = ["kernels.cuh", "faddeeva.cuh", "faddeeva_table.cuh", "voigt_constants.cuh",
+HEADERS = ["kernels.cuh", "slices.cuh", "slices_path.cuh", "faddeeva.cuh", "faddeeva_table.cuh", "voigt_constants.cuh",
            os.path.join("..", "..", "include", "dla_b200.h")]
 
 NVCC_FLAGS = [

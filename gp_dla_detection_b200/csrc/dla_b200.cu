@@ -14,8 +14,10 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "slices_path.cuh"
 
 using dla::QuasarDesc;
+using dla::sl::SliceQuasar;
 
 namespace {
 
@@ -70,6 +72,10 @@ struct Chunk {
   int64_t wu_doubles, bmat_doubles;
   int max_npad, max_P;
   bool all_ident;  // every quasar of the chunk uses the as-written gather (profile_index[j] == j)
+  // exact-slice int8 contraction (slices_path.cuh): bytes of one operand's sample planes / of the table planes
+  int64_t a_bytes, b_bytes;
+  int max_nks;
+  bool slices;     // this chunk runs K0s/K1s/K2s/K2c instead of the DMMA kernels
 };
 
 // Device-side views of one staged batch.
@@ -78,6 +84,7 @@ struct Inputs {
   const double *padded, *flux, *mu, *om, *nv, *M;
   const int32_t* pidx;
   double2* pix4;  // packed {omega2, noise, mu, flux} per kept pixel (built per chunk on the device)
+  const SliceQuasar* sq = nullptr;  // slice geometry per quasar (parallel to desc)
 };
 
 }  // namespace
@@ -89,7 +96,7 @@ struct dla_ctx {
   std::string err;
   cudaStream_t s_in = nullptr, s_out = nullptr;  // copy streams: H2D ahead of, D2H behind, the compute stream
   cudaEvent_t ev[8]{};
-  std::vector<cudaEvent_t> ev_time;   // 5 timing events per chunk
+  std::vector<cudaEvent_t> ev_time;   // NTEV timing events per chunk
   std::vector<cudaEvent_t> ev_sync;   // 2 ordering events per chunk: inputs resident, kernels done
   std::vector<Chunk> chunk_copy;      // host-side copy of the plan the events belong to
   // host pointers of the batch being staged chunk by chunk (valid during dla_eval_batch only)
@@ -126,6 +133,10 @@ struct dla_ctx {
   bool force_tile_k2 = false;        // DLA_B200_K2=tile: one CTA per tile (contract_chol_kernel)
   bool k2_rowsplit = false;          // DLA_B200_K2=rowsplit: contract_chol_rowsplit_kernel
   bool use_fused = false;            // DLA_B200_FUSED=1: fused_voigt_contract_kernel (W/U never leave the SM)
+  bool use_slices = true;            // DLA_B200_CONTRACT=dmma turns the int8 tcgen05 contraction off (FP64 DMMA kernels)
+  int k2s_mode = 0;                  // DLA_B200_K2S_MODE=1/2: diagnosis builds of the contraction (no MMA / no loads)
+  std::vector<SliceQuasar> h_sq;
+  DevBuf d_sq, d_isc, d_csc, d_btab, d_tau, d_colscale;
   int num_sms = 148;
   // staged batch
   int64_t Q = 0;
@@ -195,12 +206,86 @@ static int k1_warps_for(int raw_stride) {
   return w;
 }
 
+constexpr int NTEV = 6;  // timing events per chunk: start, tables, Voigt, contraction, Cholesky, reduction
+
+// The exact-slice path of one chunk (slices_path.cuh): K0s tables, K1s Voigt -> int8 planes, K2s tcgen05 contraction,
+// K2c Cholesky rows, K3 reduction.  Same outputs as launch_chunk.
+static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S, int k, const double* d_offset,
+                               const double* d_nhi, const int32_t* d_perm, double* sample_ll_chunk, double* ll_no,
+                               double* ll_dla, double* lp_no, double* lp_dla, double* post, int32_t* map_index,
+                               cudaEvent_t* tev) {
+  namespace sl = dla::sl;
+  const bool time_it = tev != nullptr;
+  const int nsb = (int)((S + 1 + sl::SB - 1) / sl::SB);   // 128-sample blocks
+  cudaStream_t st = c->stream;
+  int8_t* Aw = c->d_W.as<int8_t>();
+  int8_t* Au = c->d_U.as<int8_t>();
+  int8_t* Bt = c->d_btab.as<int8_t>();
+  double* G = c->d_G.as<double>();
+  double* aux = c->d_aux.as<double>();
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[0], st));
+  {
+    dim3 grid((unsigned)((ch.max_npad + 255) / 256), (unsigned)ch.nq);
+    dla::pack_pixels_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
+    sl::pixel_scales_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, c->d_isc.as<double2>(),
+                                                  c->d_csc.as<double2>());
+    sl::table_colscale_kernel<<<dim3(sl::GCOLS, (unsigned)ch.nq), 128, 0, st>>>(
+        in.desc, ch.q0, in.M, k, c->d_csc.as<double2>(), c->d_tau.as<double>(), c->d_colscale.as<double>());
+    sl::table_slices_kernel<<<dim3((unsigned)(2 * ch.max_nks), (unsigned)ch.nq), sl::GCOLS, 0, st>>>(
+        in.desc, in.sq, ch.q0, in.M, k, c->d_csc.as<double2>(), c->d_tau.as<double>(), Bt);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[1], st));
+  const int nch = 2 * ch.max_nks;
+  const int nseg = std::min(dla::K1S_NSEG_MAX, std::max(dla::K1S_NSEG_MIN, (nch + 19) / 20));
+  {
+    const int cmax = (nch + nseg - 1) / nseg;   // 16-pixel chunks per segment
+    const int lam_cap = 16 * cmax + 8, px_cap = 16 * cmax;
+    const size_t smem = (size_t)lam_cap * 8 + (size_t)px_cap * 48 + (size_t)2 * sl::NSL * 3 * sl::K1Q_THREADS * 4;
+    if (smem > 100 * 1024) BAD_ARG(c, "a quasar has too many pixels for the Voigt kernel's shared-memory staging");
+    sl::voigt_slices_lane_kernel<<<(unsigned)((int64_t)ch.nq * 2 * nsb * nseg), sl::K1Q_THREADS, smem, st>>>(
+        in.desc, in.sq, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_isc.as<double2>(), c->d_etab256.as<double>(),
+        Aw, Au, aux, lam_cap, px_cap, nseg);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[2], st));
+  {
+    const int64_t ntiles = (int64_t)ch.nq * nsb * sl::UNITS;
+    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
+    if (c->k2s_mode == 1)
+      sl::contract_slices_tiles_kernel<1><<<grid, sl::THREADS, sl::K2S_SMEM, st>>>(in.sq, ch.q0, ch.nq, nsb, Aw, Au, Bt,
+                                                                                  c->d_colscale.as<double>(), G);
+    else if (c->k2s_mode == 2)
+      sl::contract_slices_tiles_kernel<2><<<grid, sl::THREADS, sl::K2S_SMEM, st>>>(in.sq, ch.q0, ch.nq, nsb, Aw, Au, Bt,
+                                                                                  c->d_colscale.as<double>(), G);
+    else
+      sl::contract_slices_tiles_kernel<0><<<grid, sl::THREADS, sl::K2S_SMEM, st>>>(in.sq, ch.q0, ch.nq, nsb, Aw, Au, Bt,
+                                                                                  c->d_colscale.as<double>(), G);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[3], st));
+  {
+    dim3 grid((unsigned)(nsb * (sl::SB / sl::K2C_ROWS)), (unsigned)ch.nq);
+    sl::chol_rows_kernel<<<grid, sl::K2C_ROWS * 4, sl::K2C_SMEM, st>>>(in.desc, ch.q0, nsb, S, G, aux, d_perm, sample_ll_chunk,
+                                                                      ll_no, k, nseg);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[4], st));
+  if (S > 0 && ll_dla) {
+    dla::reduce_kernel<<<(unsigned)ch.nq, 256, 0, st>>>(in.desc, ch.q0, S, sample_ll_chunk, ll_no, ll_dla, lp_no,
+                                                         lp_dla, post, map_index);
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[5], st));
+  CU_TRY(c, cudaGetLastError());
+  c->timing.launches += (S > 0 && ll_dla) ? 8 : 7;
+  c->timing.contraction = 1;
+  return DLA_OK;
+}
+
 // Runs K0..K3 for one chunk of quasars on ctx->stream. sample_ll_chunk: [nq][S].
 static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S, int k, int num_lines,
                         const double* d_offset, const double* d_nhi, const int32_t* d_perm, double* sample_ll_chunk, double* ll_no,
                         double* ll_dla, double* lp_no, double* lp_dla, double* post, int32_t* map_index,
-                        cudaEvent_t* tev /* 5 timing events or nullptr */) {
+                        cudaEvent_t* tev /* NTEV timing events or nullptr */) {
   const bool time_it = tev != nullptr;
+  if (ch.slices) return launch_chunk_slices(c, in, ch, S, k, d_offset, d_nhi, d_perm, sample_ll_chunk, ll_no, ll_dla, lp_no,
+                                            lp_dla, post, map_index, tev);
   const int nsb = (int)((S + 1 + dla::TS - 1) / dla::TS);
   const ColGeom gen = col_geom(k);
   double* W = c->d_W.as<double>();
@@ -286,11 +371,12 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
         in.desc, ch.q0, nsb, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k, nseg);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[3], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[4], st));  // the Cholesky is part of the contraction kernels on this path
   if (S > 0 && ll_dla) {
     dla::reduce_kernel<<<(unsigned)ch.nq, 256, 0, st>>>(in.desc, ch.q0, S, sample_ll_chunk, ll_no, ll_dla, lp_no,
                                                          lp_dla, post, map_index);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[4], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[5], st));
   CU_TRY(c, cudaGetLastError());
   c->timing.launches += ((S > 0 && ll_dla) ? 5 : 4) + (gen.generic ? 1 : 0);
   return DLA_OK;
@@ -299,19 +385,20 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
 // after the stream has been synchronised: per-kernel device times summed over the chunks
 static int collect_timing(dla_ctx* c, size_t nchunks) {
   for (size_t i = 0; i < nchunks; ++i) {
-    cudaEvent_t* e = &c->ev_time[5 * i];
+    cudaEvent_t* e = &c->ev_time[NTEV * i];
     float ms;
     CU_TRY(c, cudaEventElapsedTime(&ms, e[0], e[1])); c->timing.ms_phi += ms;
     CU_TRY(c, cudaEventElapsedTime(&ms, e[1], e[2])); c->timing.ms_voigt += ms;
     CU_TRY(c, cudaEventElapsedTime(&ms, e[2], e[3])); c->timing.ms_contract += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, e[3], e[4])); c->timing.ms_reduce += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, e[0], e[4])); c->timing.ms_total += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[3], e[4])); c->timing.ms_chol += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[4], e[5])); c->timing.ms_reduce += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[0], e[5])); c->timing.ms_total += ms;
   }
   return DLA_OK;
 }
 
 static int ensure_events(dla_ctx* c, size_t nchunks) {
-  while (c->ev_time.size() < 5 * nchunks) {
+  while (c->ev_time.size() < NTEV * nchunks) {
     cudaEvent_t e;
     CU_TRY(c, cudaEventCreate(&e));
     c->ev_time.push_back(e);
@@ -324,13 +411,20 @@ static int ensure_events(dla_ctx* c, size_t nchunks) {
   return DLA_OK;
 }
 
-static int ensure_workspace(dla_ctx* c, int k, int64_t wu_doubles, int64_t bmat_doubles, int nq, int64_t S, bool need_ll_chunk) {
-  const int64_t S_pad = round_up(S + 1, dla::TS);
-  CU_TRY(c, c->d_W.ensure((size_t)wu_doubles * 8));
-  CU_TRY(c, c->d_U.ensure((size_t)wu_doubles * 8));
+static int ensure_workspace(dla_ctx* c, int k, int64_t wu_doubles, int64_t bmat_doubles, int nq, int64_t S, bool need_ll_chunk,
+                            int64_t a_bytes = 0, int64_t b_bytes = 0, int nq_slices = 0) {
+  const int64_t S_pad = round_up(S + 1, dla::TS), S_pad128 = round_up(S + 1, dla::sl::SB);
+  CU_TRY(c, c->d_W.ensure((size_t)std::max<int64_t>(wu_doubles * 8, a_bytes)));
+  CU_TRY(c, c->d_U.ensure((size_t)std::max<int64_t>(wu_doubles * 8, a_bytes)));
   const ColGeom gen = col_geom(k);
   CU_TRY(c, c->d_bmat.ensure((size_t)(bmat_doubles / dla::NCOL + 1) * gen.ncol * 8));
-  CU_TRY(c, c->d_aux.ensure((size_t)nq * 2 * dla::K1S_NSEG_MAX * S_pad * 8));
+  CU_TRY(c, c->d_aux.ensure((size_t)nq * 2 * dla::K1S_NSEG_MAX * S_pad128 * 8));
+  if (nq_slices > 0) {
+    CU_TRY(c, c->d_btab.ensure((size_t)std::max<int64_t>(b_bytes, 32)));
+    CU_TRY(c, c->d_G.ensure((size_t)nq_slices * S_pad128 * dla::sl::GCOLS * 8));
+    CU_TRY(c, c->d_tau.ensure((size_t)nq_slices * dla::sl::GCOLS * 8));
+    CU_TRY(c, c->d_colscale.ensure((size_t)nq_slices * dla::sl::GCOLS * 8));
+  }
   if (gen.generic) CU_TRY(c, c->d_G.ensure((size_t)nq * S_pad * gen.ncol * 8));
   if (need_ll_chunk) CU_TRY(c, c->d_ll_chunk.ensure((size_t)std::max<int64_t>(1, (int64_t)nq * S) * 8));
   return DLA_OK;
@@ -481,9 +575,19 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     c->force_tile_k2 = k2 && strcmp(k2, "tile") == 0;
     c->k2_rowsplit = k2 && strcmp(k2, "rowsplit") == 0;
     c->num_sms = prop.multiProcessorCount;
+    const char* ct = getenv("DLA_B200_CONTRACT");
+    c->use_slices = !(ct && strcmp(ct, "dmma") == 0) && !c->use_fused && !c->force_tile_k2 && !c->k2_rowsplit;
+    const char* km = getenv("DLA_B200_K2S_MODE");
+    c->k2s_mode = km ? atoi(km) : 0;
     const char* k1 = getenv("DLA_B200_K1");
     c->force_pixel_lane_k1 = k1 && strcmp(k1, "pixel") == 0;
+    if (c->force_pixel_lane_k1) c->use_slices = false;
   }
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2S_SMEM));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2S_SMEM));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2S_SMEM));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::chol_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2C_SMEM));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
   CREATE_TRY(cudaFuncSetAttribute(dla::fused_voigt_contract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -518,6 +622,7 @@ void dla_destroy(dla_ctx* c) {
                     &c->d_nv, &c->d_M, &c->d_pix4, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
                     &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk, &c->d_G, &c->d_krank,
                     &c->d_mrest, &c->d_mmu, &c->d_mM, &c->d_mlo, &c->d_lamk, &c->d_zq,
+                    &c->d_sq, &c->d_isc, &c->d_csc, &c->d_btab, &c->d_tau, &c->d_colscale,
                     &c->t_y, &c->t_l, &c->t_nv, &c->t_x, &c->t_om2, &c->t_aux, &c->t_E, &c->t_fq, &c->t_beta, &c->t_P,
                     &c->t_A1, &c->t_S, &c->t_gp, &c->t_g, &c->t_gsc, &c->t_desc})
     b->release();
@@ -612,10 +717,25 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
   // chunk plan: W+U of a chunk fit the workspace budget; at least a few chunks when the batch is
   // large enough, so that copies of one chunk overlap the kernels of another (dla_eval_batch)
   c->chunks.clear();
+  // exact-slice contraction: eligible batches (k <= 20, three lines) plan their chunks for either kernel family; a
+  // chunk takes the slice path when all of its quasars use the as-written gather
+  namespace sl = dla::sl;
+  const bool slices_elig = c->use_slices && c->p.k <= dla::KMAX && c->p.num_lines == 3;
+  const int64_t S_pad128 = round_up(S + 1, sl::SB), nsb128 = S_pad128 / sl::SB;
+  c->h_sq.assign((size_t)Q, SliceQuasar{});
+  auto nks_of = [](const QuasarDesc& d) { return (int64_t)((std::max<int32_t>(d.n, 1) + sl::KS - 1) / sl::KS); };
+  auto quasar_bytes = [&](const QuasarDesc& d, long double gq) -> long double {
+    long double b = 16.0L * S_pad * d.npad + gq;
+    if (slices_elig) {
+      const long double a2 = 2.0L * nsb128 * nks_of(d) * sl::A_STEP7;
+      b = std::max(b, a2) + 8.0L * S_pad128 * sl::GCOLS + (long double)nks_of(d) * sl::B_QSTEP;
+    }
+    return b;
+  };
   {
     long double total = 0;
     const long double gq = col_geom(c->p.k).generic ? 8.0L * S_pad * col_geom(c->p.k).ncol : 0.0L;  // G rows
-    for (int64_t q = 0; q < Q; ++q) total += 16.0L * S_pad * c->h_desc[(size_t)q].npad + gq;
+    for (int64_t q = 0; q < Q; ++q) total += quasar_bytes(c->h_desc[(size_t)q], gq);
     const int64_t budget = c->p.workspace_bytes;
     const int64_t pipe = std::min<int64_t>(max_pipe_chunks, Q / 8);
     const int64_t nch = std::max<int64_t>(std::max<int64_t>(1, pipe), (int64_t)ceill(total / budget));
@@ -625,7 +745,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
     int64_t nq_cap = INT32_MAX;
     if (Q > 0) {
       long double max_bts = 0;
-      for (int64_t q = 0; q < Q; ++q) max_bts = std::max(max_bts, 16.0L * S_pad * c->h_desc[(size_t)q].npad + gq);
+      for (int64_t q = 0; q < Q; ++q) max_bts = std::max(max_bts, quasar_bytes(c->h_desc[(size_t)q], gq));
       const int64_t nq_budget = std::max<int64_t>(1, (int64_t)(budget / max_bts));
       if (nq_budget >= 8 && nq_budget < Q) {
         const int64_t nsb = S_pad / dla::TS;
@@ -639,11 +759,11 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
     }
     int64_t q = 0;
     while (q < Q) {
-      Chunk ch{(int)q, 0, 0, 0, 0, 0, true};
+      Chunk ch{(int)q, 0, 0, 0, 0, 0, true, 0, 0, 0, false};
       long double acc = 0;
       while (q < Q) {
         QuasarDesc& d = c->h_desc[(size_t)q];
-        const long double bts = 16.0L * S_pad * d.npad + gq;
+        const long double bts = quasar_bytes(d, gq);
         if (ch.nq > 0 && (acc + bts > budget || acc >= target || ch.nq >= nq_cap)) break;
         d.wu_off = ch.wu_doubles;
         d.bmat_off = ch.bmat_doubles;
@@ -652,10 +772,19 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
         ch.max_npad = std::max(ch.max_npad, (int)d.npad);
         ch.max_P = std::max(ch.max_P, (int)d.P);
         ch.all_ident = ch.all_ident && d.ident != 0;
+        SliceQuasar& sq = c->h_sq[(size_t)q];
+        sq.nks = (int32_t)nks_of(d);
+        sq.a_off = ch.a_bytes;
+        sq.b_off = ch.b_bytes;
+        ch.a_bytes += nsb128 * sq.nks * sl::A_STEP7;
+        ch.b_bytes += (int64_t)sq.nks * sl::B_QSTEP;
+        ch.max_nks = std::max(ch.max_nks, (int)sq.nks);
         acc += bts;
         ++ch.nq;
         ++q;
       }
+      // int32 accumulators hold 7 * 2^14 * pixels: far beyond any spectrum of the pipeline, checked all the same
+      ch.slices = slices_elig && ch.all_ident && ch.max_nks * sl::KS <= 16384;
       c->chunks.push_back(ch);
     }
   }
@@ -667,6 +796,11 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
   CU_TRY(c, need(c->d_pidx, (size_t)npix * 4));
   CU_TRY(c, need(c->d_krank, (size_t)npadtot * 4));
   CU_TRY(c, need(c->d_pix4, (size_t)npix * 32));
+  CU_TRY(c, need(c->d_sq, (size_t)Q * sizeof(SliceQuasar)));
+  if (slices_elig) {
+    CU_TRY(c, need(c->d_isc, (size_t)npix * 16));
+    CU_TRY(c, need(c->d_csc, (size_t)npix * 16));
+  }
   CU_TRY(c, need(c->d_flux, (size_t)npix * 8));
   CU_TRY(c, need(c->d_mu, (size_t)npix * 8));
   CU_TRY(c, need(c->d_om, (size_t)npix * 8));
@@ -681,14 +815,20 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
   CU_TRY(c, c->d_post.ensure(2 * q8));
   CU_TRY(c, c->d_map.ensure(q8));
   {
-    int64_t wu = 0, bm = 0;
-    int nq = 0;
+    int64_t wu = 0, bm = 0, ab = 0, bb = 0;
+    int nq = 0, nqs = 0;
     for (const Chunk& ch : c->chunks) {
       wu = std::max(wu, ch.wu_doubles);
       bm = std::max(bm, ch.bmat_doubles);
       nq = std::max(nq, ch.nq);
+      if (ch.slices) {
+        ab = std::max(ab, ch.a_bytes);
+        bb = std::max(bb, ch.b_bytes);
+        nqs = std::max(nqs, ch.nq);
+      }
     }
-    int rc = ensure_workspace(c, c->p.k, std::max<int64_t>(wu, 2), std::max<int64_t>(bm, 2), std::max(nq, 1), S, !c->p.store_sample_ll);
+    int rc = ensure_workspace(c, c->p.k, std::max<int64_t>(wu, 2), std::max<int64_t>(bm, 2), std::max(nq, 1), S,
+                              !c->p.store_sample_ll, ab, bb, nqs);
     if (rc != DLA_OK) return rc;
   }
   int rc = ensure_events(c, std::max<size_t>(1, c->chunks.size()));
@@ -710,7 +850,10 @@ static int upload_chunk(dla_ctx* c, size_t i, cudaStream_t st) {
     c->timing.h2d_bytes += (int64_t)bytes;
     return cudaMemcpyAsync((char*)b.p + off_bytes, (const char*)src + off_bytes, bytes, cudaMemcpyHostToDevice, st);
   };
-  if (i == 0) CU_TRY(c, up(c->d_desc, c->h_desc.data(), 0, (size_t)c->Q * sizeof(QuasarDesc)));
+  if (i == 0) {
+    CU_TRY(c, up(c->d_desc, c->h_desc.data(), 0, (size_t)c->Q * sizeof(QuasarDesc)));
+    CU_TRY(c, up(c->d_sq, c->h_sq.data(), 0, (size_t)c->Q * sizeof(SliceQuasar)));
+  }
   const int64_t p0 = h.pix_ptr[ch.q0], p1 = h.pix_ptr[ch.q0 + ch.nq];
   const int64_t w0 = h.pad_ptr[ch.q0], w1 = h.pad_ptr[ch.q0 + ch.nq];
   CU_TRY(c, up(c->d_padded, h.padded, (size_t)w0 * 8, (size_t)(w1 - w0) * 8));
@@ -735,7 +878,7 @@ static int run_chunk(dla_ctx* c, size_t i) {
   const int64_t S = c->p.num_samples;
   Inputs in{c->d_desc.as<QuasarDesc>(), c->d_padded.as<double>(), c->d_flux.as<double>(), c->d_mu.as<double>(),
             c->d_om.as<double>(), c->d_nv.as<double>(), c->d_M.as<double>(), c->d_pidx.as<int32_t>(),
-            c->d_pix4.as<double2>()};
+            c->d_pix4.as<double2>(), c->d_sq.as<SliceQuasar>()};
   CU_TRY(c, cudaStreamWaitEvent(c->stream, c->ev_sync[2 * i], 0));
   if (c->dev_prep) {
     const dla_prep_params& pp = c->prep;
@@ -751,7 +894,7 @@ static int run_chunk(dla_ctx* c, size_t i) {
   int rc = launch_chunk(c, in, ch, S, c->p.k, c->p.num_lines, c->d_offset.as<double>(), c->d_nhi.as<double>(),
                         c->d_perm.as<int32_t>(), ll_chunk, c->d_ll_no.as<double>(), c->d_ll_dla.as<double>(),
                         c->d_lp_no.as<double>(), c->d_lp_dla.as<double>(), c->d_post.as<double>(),
-                        c->d_map.as<int32_t>(), &c->ev_time[5 * i]);
+                        c->d_map.as<int32_t>(), &c->ev_time[NTEV * i]);
   if (rc != DLA_OK) return rc;
   CU_TRY(c, cudaEventRecord(c->ev_sync[2 * i + 1], c->stream));
   c->timing.chunks++;
@@ -1079,6 +1222,7 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
         const dla_timing& t = c->timing;
         acc.ms_phi += t.ms_phi; acc.ms_voigt += t.ms_voigt; acc.ms_contract += t.ms_contract;
         acc.ms_reduce += t.ms_reduce; acc.ms_total += t.ms_total; acc.ms_h2d += t.ms_h2d; acc.ms_d2h += t.ms_d2h;
+        acc.ms_chol += t.ms_chol; acc.contraction = std::max(acc.contraction, t.contraction);
         acc.h2d_bytes += t.h2d_bytes; acc.d2h_bytes += t.d2h_bytes; acc.chunks += t.chunks; acc.launches += t.launches;
       }
     }

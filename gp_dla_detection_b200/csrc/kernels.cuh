@@ -641,13 +641,13 @@ __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const dou
 
 // weights of the four kept pixels 4g..4g+3 from the 10-point window raw[4g .. 4g+9]
 template <bool TAIL>
-__device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int n, int jdead, const double2* px /* shared */,
-                                             double* __restrict__ wp, double* __restrict__ up, double& q0acc,
-                                             double& ldacc, double& dprod, int& esum) {
+__device__ __forceinline__ void weights_lane_core(const double (&win)[10], int g, int n, int jdead, const double2* px /* shared */,
+                                                  double (&w)[4], double (&u)[4], double& q0acc, double& ldacc, double& dprod,
+                                                  int& esum) {
   // d within 2^+-200 (integer compares on the high word): the product of four such factors and a value in
   // [1,2) cannot leave the normal range
   constexpr unsigned LO = (1023 - 200) << 20, SPAN = 400u << 20;
-  double w[4], u[4], dd[4];
+  double dd[4];
   unsigned hmin = 0xffffffffu, hmax = 0u;
 #pragma unroll
   for (int h = 0; h < 4; ++h) {
@@ -702,6 +702,13 @@ __device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int
     esum += e;
     dprod = __hiloint2double(hi - (e << 20), __double2loint(dprod));
   }
+}
+template <bool TAIL>
+__device__ __forceinline__ void weights_lane(const double (&win)[10], int g, int n, int jdead, const double2* px /* shared */,
+                                             double* __restrict__ wp, double* __restrict__ up, double& q0acc,
+                                             double& ldacc, double& dprod, int& esum) {
+  double w[4], u[4];
+  weights_lane_core<TAIL>(win, g, n, jdead, px, w, u, q0acc, ldacc, dprod, esum);
   reinterpret_cast<double2*>(wp)[0] = make_double2(w[0], w[1]);
   reinterpret_cast<double2*>(wp)[1] = make_double2(w[2], w[3]);
   reinterpret_cast<double2*>(up)[0] = make_double2(u[0], u[1]);
@@ -1045,7 +1052,7 @@ __device__ __forceinline__ int tri(int i, int l) { return ((i * (i + 1)) >> 1) +
 // row[0..210): vech(G), row[VOFF..VOFF+k): v.  Returns log p on all four lanes.
 // SYNC_AFTER_LOAD: 0 none, 1 the 256-thread named barrier (the C tile is shared by the CTA), 2 __syncwarp
 // (the rows belong to this warp only)
-template <int SYNC_AFTER_LOAD = 0>
+template <int SYNC_AFTER_LOAD = 0, int VO = VOFF>
 __device__ __forceinline__ double chol_logp_quad(const double* __restrict__ row, int k, int t, double q0, double ld,
                                                  int n) {
   constexpr int NB = KMAX;      // border row index (20)
@@ -1063,7 +1070,7 @@ __device__ __forceinline__ double chol_logp_quad(const double* __restrict__ row,
       } else if (i < NB) {
         v = (l == i) ? 1.0 : 0.0;
       } else if (i == NB) {
-        v = (l < k) ? row[VOFF + l] : (l == NB ? q0 : 0.0);
+        v = (l < k) ? row[VO + l] : (l == NB ? q0 : 0.0);
       }
       A[r][l] = v;
     }

@@ -1,0 +1,544 @@
+// slices_path.cuh -- the product path of the exact-slice int8 contraction (primitives: slices.cuh).
+//
+// For k <= 20, three lines and the as-written gather, the Woodbury contraction of log_mvnpdf_low_rank.m:22 and
+// :26-28 leaves the FP64 pipe: the Voigt kernel emits W and U directly as seven signed 8-bit slices per value
+// (same bytes as fp64, minus one), the per-quasar table [Phi | M] is sliced once, and the products run on the
+// integer tcgen05 path with int32 TMEM accumulators, one per slice diagonal.  Pipeline of a chunk of quasars:
+//
+//   pixel_scales_kernel      per-pixel power-of-two bounds c_w >= max w, c_u >= 2 max |u|          (K0s)
+//   table_colscale_kernel    column scales tau of the scaled table [Phi c_w | M c_u]               (K0s)
+//   table_slices_kernel      int8 planes of the table, UMMA K-major canonical layout               (K0s)
+//   voigt_slices_lane_kernel voigt.c:278-299 + process_qsos.m:189-193 -> int8 planes of W / c_w, U / c_u,
+//                            partial sums of r'D^-1 r and log|D| (fp64)                            (K1s)
+//   contract_slices_tiles_kernel   G = [W | U] . [Phi | M] on kind::i8 tcgen05, fp64 recombination  (K2s)
+//   chol_rows_kernel         per-sample bordered 21 x 21 Cholesky (registers, one quad per sample)  (K2c)
+//
+// Fixed point.  Sample side: t = w / c_w in [0, 1) or t = u / c_u in (-1/2, 1/2) enters a double's mantissa by ONE
+// fma with a magic constant (1.0 / 1.5): X = round(t 2^52).  X = sum_i a_i 256^(6-i) in balanced digits a_i in
+// [-128, 127], so t = sum_i a_i 2^(-8 i - 4).  Table side: b = entry / tau in [-1, 1] with 54 fractional bits,
+// b = sum_j b_j 2^(-8 j - 6).  Slice products with i + j = d share the weight 2^(-8 d - 10) and accumulate exactly
+// in int32 (|sum| <= 7 * 2^14 * pixels < 2^31 for pixels <= 18 000); pairs with i + j >= 7 are dropped.
+#ifndef GPDLA_SLICES_PATH_CUH
+#define GPDLA_SLICES_PATH_CUH
+
+#include "slices.cuh"
+
+namespace dla {
+namespace sl {
+
+constexpr int NSL = 7;                         // slices per value
+constexpr int A_STEP7 = NSL * 2 * SB * 16;     // 28 672 bytes of sample planes per K step (32 pixels, 128 samples)
+constexpr int B_STEP64 = NSL * 2 * 64 * 16;    // 14 336 bytes of table planes per K step, 64-column unit
+constexpr int B_STEP32 = NSL * 2 * 32 * 16;    //  7 168, 32-column unit
+constexpr int B_QSTEP = 3 * B_STEP64 + 2 * B_STEP32;   // table bytes per K step and quasar: 57 344
+constexpr int GCOLS = 256;                     // row of G: [0, 224) W.Phi (k (k+1) / 2 used), [224, 256) U.M (k used)
+constexpr int VOFF_S = 224;
+constexpr int UNITS = 5;                       // column units per sample block: 64, 64, 64, 32 (W planes), 32 (U planes)
+constexpr int K2S_STAGES = 5;
+constexpr int K2S_STAGE = A_STEP7 + B_STEP64;  // 43 008
+constexpr size_t K2S_SMEM = (size_t)K2S_STAGES * K2S_STAGE + 1024 + 256;
+constexpr int K1Q_THREADS = 64;                // one CTA = 64 hypotheses (half a sample block) x one spectrum segment
+
+// per quasar of the staged batch (device array parallel to QuasarDesc)
+struct SliceQuasar {
+  int64_t a_off;   // byte offset of this quasar's sample planes in the chunk's W (and U) plane buffers
+  int64_t b_off;   // byte offset of its table planes
+  int32_t nks;     // K steps = ceil(n / 32)
+  int32_t pad_;
+};
+
+// ------------------------------------------------------------------------------------------------------------
+// K0s.  Per-pixel scales.  w = a^2 / (omega2 a^2 + nu) <= 1 / (omega2 + nu) for a in [0, 1];
+// |u| = a |y - mu a| / (omega2 a^2 + nu) <= (|y| + |mu|) max_a a / (omega2 a^2 + nu), the maximum at
+// a = sqrt(nu / omega2) when that is < 1.  Powers of two, so that scaling is exact.
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double pow2_above(double x, int extra) {
+  if (!(x > 0.0) || !(x < 1.7e308)) return 1.0;   // 0, negative, NaN, inf: the value itself is already meaningless
+  int e;
+  const double f = frexp(x, &e);                   // x = f 2^e, f in [0.5, 1)
+  return ldexp(1.0, e + extra + (f > 0.98 ? 1 : 0));
+}
+__global__ void pixel_scales_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ flux,
+                                    const double* __restrict__ mu, const double* __restrict__ omega2,
+                                    const double* __restrict__ noise_variance, double2* __restrict__ isc /* {1/c_w, 1/c_u} */,
+                                    double2* __restrict__ csc /* {c_w, c_u} */) {
+  const QuasarDesc d = desc[q0 + blockIdx.y];
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= d.n) return;
+  const int64_t g = d.pix_off + j;
+  const double om = omega2[g], nv = noise_variance[g];
+  const double top = 1.0 / (om + nv);
+  const double amax = (nv < om) ? 0.5 / sqrt(om * nv) : top;
+  const double cw = pow2_above(top, 0);                              // t = w / c_w <= 0.98
+  const double cu = pow2_above((fabs(flux[g]) + fabs(mu[g])) * amax, 1);   // |t| = |u| / c_u <= 0.49
+  isc[g] = make_double2(1.0 / cw, 1.0 / cu);
+  csc[g] = make_double2(cw, cu);
+}
+
+// table entry of column c (0 <= c < 256) at pixel p, scaled by the pixel's power of two
+__device__ __forceinline__ void col_to_il(int c, int k, int& i, int& l) {
+  i = -1;
+  l = -1;
+  if (c < k * (k + 1) / 2) {
+    i = (int)((sqrt(8.0 * c + 1.0) - 1.0) * 0.5);
+    while (i * (i + 1) / 2 > c) --i;
+    while ((i + 1) * (i + 2) / 2 <= c) ++i;
+    l = c - i * (i + 1) / 2;
+  } else if (c >= VOFF_S && c < VOFF_S + k) {
+    i = c - VOFF_S;
+  }
+}
+__device__ __forceinline__ double table_entry(const double* __restrict__ Mq, int n, int p, int i, int l, double2 cs) {
+  const double mi = Mq[(int64_t)i * n + p];
+  return (l >= 0) ? (mi * Mq[(int64_t)l * n + p]) * cs.x : mi * cs.y;
+}
+// column scales: tau_c = 2^ceil(log2 max_p |entry|) (1 for an empty column, NaN if any entry is NaN: a NaN model
+// entry must poison every sample of the quasar as it does in fp64); colscale = tau 2^-10
+__global__ void table_colscale_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ M, int k,
+                                      const double2* __restrict__ csc, double* __restrict__ tau,
+                                      double* __restrict__ colscale) {
+  const QuasarDesc d = desc[q0 + blockIdx.y];
+  const int c = blockIdx.x;
+  int i, l;
+  col_to_il(c, k, i, l);
+  __shared__ double red[128];
+  double m = 0.0;
+  bool bad = false;
+  if (i >= 0) {
+    const double* Mq = M + (int64_t)k * d.pix_off;
+    for (int p = threadIdx.x; p < d.n; p += blockDim.x) {
+      const double v = fabs(table_entry(Mq, d.n, p, i, l, csc[d.pix_off + p]));
+      bad = bad || !(v == v);
+      m = fmax(m, v);
+    }
+  }
+  const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+  red[threadIdx.x] = bad ? qnan : m;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) {
+      const double a = red[threadIdx.x], b = red[threadIdx.x + o];
+      red[threadIdx.x] = (a != a || b != b) ? qnan : fmax(a, b);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double mm = red[0];
+    double t = 1.0;
+    if (mm != mm) t = mm;
+    else if (mm > 0.0) {
+      int e;
+      const double f = frexp(mm, &e);
+      t = ldexp(1.0, (f == 0.5) ? e - 1 : e);
+      if (!(t < 1.7e308)) t = qnan;   // an infinite entry: poison
+    }
+    tau[(int64_t)blockIdx.y * GCOLS + c] = t;
+    colscale[(int64_t)blockIdx.y * GCOLS + c] = t * 0.0009765625;
+  }
+}
+// planes: unit u < 3: [K step][slice][2][64 columns][16 B] at b_off + u nks B_STEP64; u = 3, 4: 32 columns, at
+// b_off + 3 nks B_STEP64 + (u - 3) nks B_STEP32.  One thread per (column, 16-pixel chunk); pixels >= n are zero.
+__global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar* __restrict__ sq, int q0,
+                                    const double* __restrict__ M, int k, const double2* __restrict__ csc,
+                                    const double* __restrict__ tau, int8_t* __restrict__ planes) {
+  const QuasarDesc d = desc[q0 + blockIdx.y];
+  const SliceQuasar s = sq[q0 + blockIdx.y];
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nch = s.nks * 2;
+  if (idx >= GCOLS * nch) return;
+  const int col = idx % GCOLS, ch = idx / GCOLS;   // consecutive threads = consecutive columns (contiguous 16-byte pieces)
+  int i, l;
+  col_to_il(col, k, i, l);
+  const double tc = tau[(int64_t)blockIdx.y * GCOLS + col];
+  const double it = 1.0 / tc;   // a power of two; NaN -> zeros here, the NaN travels in colscale
+  const double* Mq = M + (int64_t)k * d.pix_off;
+  uint64_t dig[16];
+#pragma unroll
+  for (int p = 0; p < 16; ++p) {
+    const int px = ch * 16 + p;
+    double v = 0.0;
+    if (i >= 0 && px < d.n) v = table_entry(Mq, d.n, px, i, l, csc[d.pix_off + px]) * it;
+    dig[p] = balanced_digits<NSL>(to_fixed<NSL>(v == v ? v : 0.0));
+  }
+  const int u = (col < 192) ? (col >> 6) : (col < VOFF_S ? 3 : 4);
+  const int N = (u < 3) ? 64 : 32;
+  const int cc = (u < 3) ? (col & 63) : (col & 31);
+  const int64_t ubase = (u < 3) ? (int64_t)u * s.nks * B_STEP64 : (int64_t)3 * s.nks * B_STEP64 + (int64_t)(u - 3) * s.nks * B_STEP32;
+  const int ks = ch >> 1, c2 = ch & 1;
+  int8_t* base = planes + s.b_off + ubase + (int64_t)ks * (NSL * 2 * N * 16) + (int64_t)c2 * (N * 16) + cc * 16;
+#pragma unroll
+  for (int sl_ = 0; sl_ < NSL; ++sl_) {
+    uint32_t w[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t v = 0;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) v |= (uint32_t)((dig[4 * q + b] >> (8 * (NSL - 1 - sl_))) & 0xffu) << (8 * b);
+      w[q] = v;
+    }
+    *reinterpret_cast<uint4*>(base + (int64_t)sl_ * (2 * N * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K1s.  voigt_weights_lane_kernel (kernels.cuh) with the slice emission: a lane owns one hypothesis and walks one
+// segment of the spectrum; segments are whole 16-pixel chunks.  Every step yields four pixels, i.e. one 32-bit
+// word of each of the 14 sixteen-byte pieces (7 slices of W, 7 of U) the lane owns; the pieces are complete after
+// four steps and leave as 16-byte stores, 512 contiguous bytes per warp and piece.  The words of the first three
+// steps wait in a per-lane shared-memory slot ([piece][step][lane]: conflict-free both ways), not in registers.
+//   planes: a_off + ((sb * nks + ks) * 7 + slice) * 4096 + (chunk & 1) * 2048 + row * 16
+// ------------------------------------------------------------------------------------------------------------
+// m[h] = fma(value, 1 / scale, MAGIC): bits(m) - bits(MAGIC) = X = round(t 2^52) (two's complement, |X| < 2^52);
+// digits of X, slice i = byte 6 - i; out[i] = the four pixels' slice-i bytes
+template <uint32_t MAGIC_HI>
+__device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NSL]) {
+  constexpr uint64_t C = 0x0000808080808080ull;
+  constexpr uint64_t K = C - ((uint64_t)MAGIC_HI << 32);
+  uint32_t lo[4], hi[4];
+#pragma unroll
+  for (int h = 0; h < 4; ++h) {
+    const uint64_t b = ((uint64_t)__double_as_longlong(m[h]) + K) ^ C;
+    lo[h] = (uint32_t)b;
+    hi[h] = (uint32_t)(b >> 32);
+  }
+  const uint32_t t0 = __byte_perm(lo[0], lo[1], 0x5140), t1 = __byte_perm(lo[2], lo[3], 0x5140);
+  const uint32_t t2 = __byte_perm(lo[0], lo[1], 0x7362), t3 = __byte_perm(lo[2], lo[3], 0x7362);
+  out[6] = __byte_perm(t0, t1, 0x5410);
+  out[5] = __byte_perm(t0, t1, 0x7632);
+  out[4] = __byte_perm(t2, t3, 0x5410);
+  out[3] = __byte_perm(t2, t3, 0x7632);
+  const uint32_t t4 = __byte_perm(hi[0], hi[1], 0x5140), t5 = __byte_perm(hi[2], hi[3], 0x5140);
+  const uint32_t t6 = __byte_perm(hi[0], hi[1], 0x0062), t7 = __byte_perm(hi[2], hi[3], 0x0062);
+  out[2] = __byte_perm(t4, t5, 0x5410);
+  out[1] = __byte_perm(t4, t5, 0x7632);
+  out[0] = __byte_perm(t6, t7, 0x5410);
+}
+
+#ifndef DLA_K1Q_MINB
+#define DLA_K1Q_MINB 6   // resident CTAs per SM (6 -> 168 registers)
+#endif
+__global__ void __launch_bounds__(K1Q_THREADS, DLA_K1Q_MINB)
+voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar* __restrict__ sq, int q0, int nsb /* 128-sample blocks */,
+                         int64_t S, const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
+                         const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
+                         const double2* __restrict__ isc, const double* __restrict__ etab256, int8_t* __restrict__ Wplanes,
+                         int8_t* __restrict__ Uplanes, double* __restrict__ aux, int lam_cap, int px_cap, int nseg) {
+  extern __shared__ __align__(16) double k1q_smem[];
+  __shared__ double etab_s[256];
+  const int nsb64 = 2 * nsb;
+  const int seg = blockIdx.x % nseg;
+  const int tile = blockIdx.x / nseg;
+  const int ql = tile / nsb64, sb64 = tile % nsb64;
+  const QuasarDesc d = desc[q0 + ql];
+  const SliceQuasar sqq = sq[q0 + ql];
+  const int tid = threadIdx.x;
+  const int n = d.n, Pm1 = d.P - 1;
+  const int nch = 2 * sqq.nks;                                            // 16-pixel chunks
+  const int c0 = (int)(((int64_t)seg * nch) / nseg), c1 = (int)(((int64_t)(seg + 1) * nch) / nseg);
+  const int g0 = 4 * c0, g1 = 4 * c1;                                     // groups of four pixels
+  const int lbase = max(4 * g0 - 2, 0), llast = min(4 * g1 + 5, Pm1);
+  const int j0 = min(4 * g0, n), j1 = min(4 * g1, n);                     // kept pixels this segment emits
+  const int nsteps = (g1 > g0) ? g1 - g0 + 2 : 0;
+  double* lam_s = k1q_smem;
+  double2* px_s = reinterpret_cast<double2*>(k1q_smem + lam_cap);
+  double2* sc_s = px_s + 2 * px_cap;
+  uint32_t* stg_s = reinterpret_cast<uint32_t*>(sc_s + px_cap) + tid;   // [14 pieces][3 steps][64 lanes]
+  for (int i = tid; i < 256; i += K1Q_THREADS) etab_s[i] = etab256[i];
+  {
+    const double* lam_g = padded_wavelengths + d.pad_off;
+    for (int i = tid; i < 4 * nsteps; i += K1Q_THREADS) lam_s[i] = __ldg(lam_g + min(max(4 * g0 - 2 + i, lbase), llast));
+    const double2* px_g = pix4 + 2 * (d.pix_off + j0);
+    for (int i = tid; i < 2 * (j1 - j0); i += K1Q_THREADS) px_s[i] = __ldg(px_g + i);
+    const double2* sc_g = isc + d.pix_off + j0;
+    for (int i = tid; i < j1 - j0; i += K1Q_THREADS) sc_s[i] = __ldg(sc_g + i);
+  }
+  __syncthreads();
+  const int64_t s = (int64_t)sb64 * K1Q_THREADS + tid;
+  const bool real = s < S;
+  const double off = real ? offset_sorted[s] : 0.0;       // process_qsos.m:163-165, separately rounded
+  const double N = real ? nhi_sorted[s] : 0.0;
+  const double z = __dadd_rn(d.min_z, __dmul_rn(__dsub_rn(d.max_z, d.min_z), off));
+  const double opz = __dadd_rn(1.0, z);
+  double mult[3], ncw[3], nc1[3], nc2[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    mult[j] = DLA_C_CGS / __dmul_rn(dla_transition_wavelengths[j], opz) / 1e8;  // voigt.c:278-279
+    ncw[j] = -N * g_lines.cwT[j];
+    nc1[j] = ncw[j] * g_lines.g1p[j];
+    nc2[j] = ncw[j] * g_lines.gq[2];
+  }
+  const double2* px = px_s - 2 * j0;   // indexed by 2 * kept pixel
+  const double2* sc = sc_s - j0;       // indexed by kept pixel
+  const int jdead = (j1 > j0) ? j0 : 0;  // a live pixel of this segment stands in for dead ones (values discarded)
+  const int gfull = n >> 2;
+  const int64_t S_pad = (int64_t)nsb * SB;
+  const int row = (sb64 & 1) * K1Q_THREADS + tid;
+  const int64_t sb_base = sqq.a_off + (int64_t)(sb64 >> 1) * sqq.nks * A_STEP7 + row * 16;
+  int8_t* wq = Wplanes + sb_base;
+  int8_t* uq = Uplanes + sb_base;
+
+  double q0acc = 0.0, ldacc = 0.0, dprod = 1.0;
+  int esum = 0;
+  double win[10];
+#pragma unroll
+  for (int t = 0; t < 10; ++t) win[t] = 0.0;
+  const bool have_px = j1 > j0;   // a segment wholly beyond n (padding chunks) emits zeros
+  for (int st = 0; st < nsteps; ++st) {
+    double l4[4], r4[4];
+    {
+      const double2 la = reinterpret_cast<const double2*>(lam_s)[2 * st], lb = reinterpret_cast<const double2*>(lam_s)[2 * st + 1];
+      l4[0] = la.x, l4[1] = la.y, l4[2] = lb.x, l4[3] = lb.y;
+    }
+    raw_lane<4>(l4, mult, ncw, nc1, nc2, N, etab_s, r4);
+#pragma unroll
+    for (int t = 0; t < 6; ++t) win[t] = win[t + 4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) win[6 + h] = r4[h];
+    if (st >= 2) {
+      const int g = g0 + st - 2;
+      double w[4], u[4];
+      if (g < gfull) weights_lane_core<false>(win, g, n, jdead, px, w, u, q0acc, ldacc, dprod, esum);
+      else if (have_px) weights_lane_core<true>(win, g, n, jdead, px, w, u, q0acc, ldacc, dprod, esum);
+      else {
+#pragma unroll
+        for (int h = 0; h < 4; ++h) w[h] = u[h] = 0.0;
+      }
+      double mw[4], mu_[4];
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const int j = 4 * g + h;
+        const double2 is = have_px ? sc[(j < n) ? j : jdead] : make_double2(0.0, 0.0);
+        mw[h] = fma(w[h], is.x, 1.0);
+        mu_[h] = fma(u[h], is.y, 1.5);
+      }
+      uint32_t nw[NSL], nu[NSL];
+      digits4<0x3FF00000u>(mw, nw);
+      digits4<0x3FF80000u>(mu_, nu);
+      const int qs = g & 3;
+      if (qs < 3) {
+        uint32_t* slot = stg_s + qs * K1Q_THREADS;
+#pragma unroll
+        for (int i = 0; i < NSL; ++i) {
+          slot[i * 3 * K1Q_THREADS] = nw[i];
+          slot[(NSL + i) * 3 * K1Q_THREADS] = nu[i];
+        }
+      } else {
+        const int ch = g >> 2;
+        const int64_t o = (int64_t)(ch >> 1) * A_STEP7 + (ch & 1) * (SB * 16);
+#pragma unroll
+        for (int i = 0; i < NSL; ++i) {
+          const uint32_t* a = stg_s + i * 3 * K1Q_THREADS;
+          const uint32_t* b = stg_s + (NSL + i) * 3 * K1Q_THREADS;
+          *reinterpret_cast<uint4*>(wq + o + i * (2 * SB * 16)) = make_uint4(a[0], a[K1Q_THREADS], a[2 * K1Q_THREADS], nw[i]);
+          *reinterpret_cast<uint4*>(uq + o + i * (2 * SB * 16)) = make_uint4(b[0], b[K1Q_THREADS], b[2 * K1Q_THREADS], nu[i]);
+        }
+      }
+    }
+  }
+  ldacc += fma((double)esum, 0.693147180559945309417232, log(dprod));
+  double* auxq = aux + (int64_t)ql * 2 * nseg * S_pad;
+  auxq[(int64_t)seg * S_pad + s] = q0acc;
+  auxq[(int64_t)(nseg + seg) * S_pad + s] = ldacc;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K2s.  Persistent: CTA b walks the work items t = b, b + gridDim.x, ...; item t = ((ql * nsb) + sb) * 5 + unit, so the
+// five units of a sample block run at the same time on neighbouring SMs and share the block's planes through L2.
+// Warp 0: TMA producer (two 1-D bulk copies per K step), warp 1: MMA issue (28 kind::i8 MMAs per K step), warps
+// 2..5: epilogue (TMEM -> fp64 -> G).  MODE 1 / 2 (diagnosis): no MMA / no loads after the first ring fill.
+// ------------------------------------------------------------------------------------------------------------
+struct K2sTile {
+  const int8_t* a;
+  const int8_t* b;
+  int nks, N, ql, sb, col0;
+};
+__device__ __forceinline__ K2sTile k2s_decode(int t, const SliceQuasar* __restrict__ sq, int q0, int nsb, const int8_t* Aw,
+                                              const int8_t* Au, const int8_t* Bt) {
+  K2sTile r;
+  const int per = nsb * UNITS;
+  r.ql = t / per;
+  const int rem = t - r.ql * per;
+  r.sb = rem / UNITS;
+  const int u = rem - r.sb * UNITS;
+  const SliceQuasar s = sq[q0 + r.ql];
+  r.nks = s.nks;
+  r.N = (u < 3) ? 64 : 32;
+  r.col0 = (u < 3) ? 64 * u : (u == 3 ? 192 : VOFF_S);
+  r.a = ((u == 4) ? Au : Aw) + s.a_off + (int64_t)r.sb * s.nks * A_STEP7;
+  r.b = Bt + s.b_off + ((u < 3) ? (int64_t)u * s.nks * B_STEP64 : (int64_t)3 * s.nks * B_STEP64 + (int64_t)(u - 3) * s.nks * B_STEP32);
+  return r;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(THREADS, 1)
+contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq, int nsb, const int8_t* __restrict__ Aw,
+                             const int8_t* __restrict__ Au, const int8_t* __restrict__ Bt, const double* __restrict__ colscale,
+                             double* __restrict__ G) {
+  extern __shared__ unsigned char sl_smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(sl_smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)K2S_STAGES * K2S_STAGE);
+  uint64_t* empty = full + K2S_STAGES;
+  uint64_t* tfull = empty + K2S_STAGES;
+  uint64_t* tempty = tfull + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ntiles = nq * nsb * UNITS;
+
+  if (tid == 0) {
+    for (int s = 0; s < K2S_STAGES; ++s) {
+      bar_init(&full[s], 1);
+      bar_init(&empty[s], 1);
+    }
+    bar_init(tfull, 1);
+    bar_init(tempty, 4);   // one arrive per epilogue warp
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const K2sTile tl = k2s_decode(t, sq, q0, nsb, Aw, Au, Bt);
+        const uint32_t bstep = (uint32_t)(NSL * 2 * 16) * tl.N;
+        for (int ks = 0; ks < tl.nks; ++ks, ++it) {
+          const int st = it % K2S_STAGES;
+          bar_wait(&empty[st], ((it / K2S_STAGES) & 1) ^ 1);
+          unsigned char* dst = smem + (size_t)st * K2S_STAGE;
+          if (MODE == 2 && it >= (uint32_t)K2S_STAGES) {
+            bar_arrive(&full[st]);
+          } else {
+            bar_expect_tx(&full[st], A_STEP7 + bstep);
+            bulk_load(dst, tl.a + (int64_t)ks * A_STEP7, A_STEP7, &full[st]);
+            bulk_load(dst + A_STEP7, tl.b + (int64_t)ks * bstep, bstep, &full[st]);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    uint32_t it = 0, tcount = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
+      const K2sTile tl = k2s_decode(t, sq, q0, nsb, Aw, Au, Bt);
+      const uint32_t N = (uint32_t)tl.N;
+      const uint32_t idesc = idesc_i8(SB, tl.N);
+      bar_wait(tempty, (tcount & 1) ^ 1);   // the epilogue has drained the previous tile's accumulators
+      tc_fence_after();
+      for (int ks = 0; ks < tl.nks; ++ks, ++it) {
+        const int st = it % K2S_STAGES;
+        bar_wait(&full[st], (it / K2S_STAGES) & 1);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t abase = s32(smem + (size_t)st * K2S_STAGE);
+          const uint32_t bbase = abase + A_STEP7;
+          const uint32_t first = (ks == 0) ? 0u : 1u;
+          if (MODE != 1) {
+#pragma unroll
+            for (int i = 0; i < NSL; ++i) {
+              const uint64_t ad = smem_desc(abase + i * (2 * SB * 16), SB * 16, 128);
+#pragma unroll
+              for (int j = 0; j + i < NSL; ++j) {
+                const uint64_t bd = smem_desc(bbase + j * (2 * 16) * N, 16 * N, 128);
+                umma_i8(tmem_base + (uint32_t)(i + j) * N, ad, bd, idesc, (i == 0) ? first : 1u);
+              }
+            }
+          }
+          umma_commit(&empty[st]);
+          if (ks == tl.nks - 1) umma_commit(tfull);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    const int quarter = warp & 3;             // TMEM lanes [32 q, 32 q + 32) belong to the warps with warp % 4 == q
+    const int row = quarter * 32 + lane;
+    const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const int64_t S_pad = (int64_t)nsb * SB;
+    uint32_t tcount = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
+      const K2sTile tl = k2s_decode(t, sq, q0, nsb, Aw, Au, Bt);
+      bar_wait(tfull, tcount & 1);
+      tc_fence_after();
+      double* grow = G + ((int64_t)tl.ql * S_pad + (int64_t)tl.sb * SB + row) * GCOLS + tl.col0;
+      const double* cs = colscale + (int64_t)tl.ql * GCOLS + tl.col0;
+      const int nc8 = tl.N / 8;
+#pragma unroll 1
+      for (int c8 = 0; c8 < nc8; ++c8) {
+        uint32_t r[NSL][8];
+#pragma unroll
+        for (int dgn = 0; dgn < NSL; ++dgn) tmem_ld8(tlane + (uint32_t)(dgn * tl.N + c8 * 8), r[dgn]);
+        tmem_ld_wait();
+        double out[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          double v = i32_to_f64(r[NSL - 1][c]);
+#pragma unroll
+          for (int dgn = NSL - 2; dgn >= 0; --dgn) v = fma(v, 0.00390625, i32_to_f64(r[dgn][c]));
+          out[c] = v * __ldg(cs + c8 * 8 + c);
+        }
+#pragma unroll
+        for (int c = 0; c < 8; c += 2) *reinterpret_cast<double2*>(grow + c8 * 8 + c) = make_double2(out[c], out[c + 1]);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) bar_arrive(tempty);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K2c.  log_mvnpdf_low_rank.m:23-32 from the rows of G: one quad of lanes per sample (chol_logp_quad, kernels.cuh),
+// 32 samples per CTA, their rows (2 KB each) brought in by 32 bulk copies into padded shared-memory rows.
+// ------------------------------------------------------------------------------------------------------------
+constexpr int K2C_ROWS = 32;
+constexpr int K2C_LD = GCOLS + 2;   // padded row (doubles): the eight samples of a warp start in different banks
+constexpr size_t K2C_SMEM = (size_t)K2C_ROWS * K2C_LD * 8 + 16;
+__global__ void __launch_bounds__(K2C_ROWS * 4, 2)
+chol_rows_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb /* 128-sample blocks */, int64_t S,
+                 const double* __restrict__ G, const double* __restrict__ aux, const int32_t* __restrict__ perm,
+                 double* __restrict__ sample_ll /* [nq][S], caller order */, double* __restrict__ ll_no, int k, int nseg) {
+  extern __shared__ __align__(16) unsigned char k2c_smem[];
+  double* rows = reinterpret_cast<double*>(k2c_smem);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(k2c_smem + (size_t)K2C_ROWS * K2C_LD * 8);
+  const int ql = blockIdx.y;
+  const QuasarDesc d = desc[q0 + ql];
+  const int64_t S_pad = (int64_t)nsb * SB;
+  const int64_t s0 = (int64_t)blockIdx.x * K2C_ROWS;
+  if (s0 > S) return;   // rows beyond the no-DLA pseudo-sample are padding
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    bar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0) {
+    bar_expect_tx(bar, K2C_ROWS * GCOLS * 8);
+    const double* src = G + ((int64_t)ql * S_pad + s0) * GCOLS;
+    for (int r = 0; r < K2C_ROWS; ++r) bulk_load(rows + (size_t)r * K2C_LD, src + (size_t)r * GCOLS, GCOLS * 8, bar);
+  }
+  const int srow = tid >> 2, t = tid & 3;
+  const int64_t s = s0 + srow;
+  double q0v, ldv;
+  aux_sums(aux, ql, nseg, S_pad, s, q0v, ldv);
+  bar_wait(bar, 0);
+  const double lp = chol_logp_quad<0, VOFF_S>(rows + (size_t)srow * K2C_LD, k, t, q0v, ldv, d.n);
+  if (t == 0) {
+    if (s < S) sample_ll[(int64_t)ql * S + perm[s]] = lp;
+    else if (s == S) ll_no[q0 + ql] = lp;
+  }
+}
+
+}  // namespace sl
+}  // namespace dla
+#endif

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define DLA_B200_ABI_VERSION 1
+#define DLA_B200_ABI_VERSION 2
 
 typedef enum {
   DLA_OK = 0,
@@ -56,6 +56,8 @@ typedef struct {
   int64_t launches;      /* kernels launched                              */
   int64_t h2d_bytes, d2h_bytes;
   int64_t chunks;        /* quasar chunks the batch was split into        */
+  double ms_chol;        /* K2c Cholesky rows (int8 slice path; 0 on the DMMA path, where it is K2's epilogue) */
+  int64_t contraction;   /* 0: FP64 DMMA kernels, 1: exact-slice int8 tcgen05 contraction */
 } dla_timing;
 
 int dla_abi_version(void);

@@ -24,7 +24,7 @@ def test_library_exports_every_symbol_the_header_declares():
     lib = _lib.load()
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.dla_abi_version() == 1
+    assert lib.dla_abi_version() == 2
 
 
 def test_no_cpu_fallback_create_fails_loudly_without_a_device():
