@@ -135,8 +135,21 @@ struct dla_ctx {
   bool use_fused = false;            // DLA_B200_FUSED=1: fused_voigt_contract_kernel (W/U never leave the SM)
   bool use_slices = true;            // DLA_B200_CONTRACT=dmma turns the int8 tcgen05 contraction off (FP64 DMMA kernels)
   int k2s_mode = 0;                  // DLA_B200_K2S_MODE=1/2: diagnosis builds of the contraction (no MMA / no loads)
+  int k2s_stages = 5;                // DLA_B200_K2S_STAGES=3/5: ring depth of the contraction when it runs alone
+  int overlap_chunks = 16;           // DLA_B200_OVERLAP_CHUNKS: chunks an overlapped batch is split into (at most)
+  bool overlap = true;               // DLA_B200_OVERLAP=0: contraction of chunk i NOT run under the Voigt kernel of chunk i + 1
   std::vector<SliceQuasar> h_sq;
-  DevBuf d_sq, d_isc, d_csc, d_btab, d_tau, d_colscale;
+  DevBuf d_sq, d_isc, d_csc;
+  // slice-path workspace of one chunk: sample planes, table planes and scales, partial sums; two sets when chunks overlap
+  struct SliceSet {
+    DevBuf W, U, btab, tau, colscale, aux;
+    cudaEvent_t planes_ready = nullptr, done = nullptr;
+    bool busy = false;   // `done` has been recorded and not yet waited for by the host
+  } sset[2];
+  cudaStream_t stream2 = nullptr;    // contraction stream of the overlapped slice path (higher priority)
+  DevBuf d_trace;                    // DLA_B200_TRACE=<file>: CTA residency trace of the slice kernels (diagnosis)
+  std::string trace_path;
+  int slice_chunks = 0;
   int num_sms = 148;
   // staged batch
   int64_t Q = 0;
@@ -206,10 +219,25 @@ static int k1_warps_for(int raw_stride) {
   return w;
 }
 
-constexpr int NTEV = 6;  // timing events per chunk: start, tables, Voigt, contraction, Cholesky, reduction
+// timing events per chunk: [0] start, [1] tables done, [2] Voigt done, [3] contraction start, [4] contraction done,
+// [5] Cholesky done, [6] reduction done ([0..2] on the compute stream, [3..6] on the stream the contraction runs on)
+constexpr int NTEV = 7;
 
-// The exact-slice path of one chunk (slices_path.cuh): K0s tables, K1s Voigt -> int8 planes, K2s tcgen05 contraction,
-// K2c Cholesky rows, K3 reduction.  Same outputs as launch_chunk.
+template <typename... Args>
+static void launch_k2s(int mode, int stages, unsigned grid, cudaStream_t st, Args... args) {
+  namespace sl = dla::sl;
+  if (mode == 1 && stages == 3) sl::contract_slices_tiles_kernel<1, 3><<<grid, sl::THREADS, sl::k2s_smem(3), st>>>(args...);
+  else if (mode == 2 && stages == 3) sl::contract_slices_tiles_kernel<2, 3><<<grid, sl::THREADS, sl::k2s_smem(3), st>>>(args...);
+  else if (mode == 1) sl::contract_slices_tiles_kernel<1, 5><<<grid, sl::THREADS, sl::k2s_smem(5), st>>>(args...);
+  else if (mode == 2) sl::contract_slices_tiles_kernel<2, 5><<<grid, sl::THREADS, sl::k2s_smem(5), st>>>(args...);
+  else if (stages == 3) sl::contract_slices_tiles_kernel<0, 3><<<grid, sl::THREADS, sl::k2s_smem(3), st>>>(args...);
+  else sl::contract_slices_tiles_kernel<0, 5><<<grid, sl::THREADS, sl::k2s_smem(5), st>>>(args...);
+}
+
+// The exact-slice path of one chunk (slices_path.cuh): K0s tables and K1s Voigt -> int8 planes on the compute stream,
+// then K2s tcgen05 contraction, K2c Cholesky rows and K3 reduction on the contraction stream.  With overlap on, the
+// contraction stream is a second (higher-priority) stream and the plane / table / partial-sum buffers alternate
+// between two sets, so the tensor-pipe work of chunk i runs under the FP64-pipe work of chunk i + 1 on the same SMs.
 static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S, int k, const double* d_offset,
                                const double* d_nhi, const int32_t* d_perm, double* sample_ll_chunk, double* ll_no,
                                double* ll_dla, double* lp_no, double* lp_dla, double* post, int32_t* map_index,
@@ -217,61 +245,67 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
   namespace sl = dla::sl;
   const bool time_it = tev != nullptr;
   const int nsb = (int)((S + 1 + sl::SB - 1) / sl::SB);   // 128-sample blocks
-  cudaStream_t st = c->stream;
-  int8_t* Aw = c->d_W.as<int8_t>();
-  int8_t* Au = c->d_U.as<int8_t>();
-  int8_t* Bt = c->d_btab.as<int8_t>();
+  const bool ov = c->overlap;
+  cudaStream_t sa = c->stream, sb = ov ? c->stream2 : c->stream;
+  dla_ctx::SliceSet& set = c->sset[ov ? (c->slice_chunks & 1) : 0];
+  c->slice_chunks++;
+  int8_t* Aw = set.W.as<int8_t>();
+  int8_t* Au = set.U.as<int8_t>();
+  int8_t* Bt = set.btab.as<int8_t>();
   double* G = c->d_G.as<double>();
-  double* aux = c->d_aux.as<double>();
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[0], st));
+  double* aux = set.aux.as<double>();
+  if (ov && set.busy) CU_TRY(c, cudaStreamWaitEvent(sa, set.done, 0));   // the chunk that last used this set has finished
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[0], sa));
   {
     dim3 grid((unsigned)((ch.max_npad + 255) / 256), (unsigned)ch.nq);
-    dla::pack_pixels_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
-    sl::pixel_scales_kernel<<<grid, 256, 0, st>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, c->d_isc.as<double2>(),
+    dla::pack_pixels_kernel<<<grid, 256, 0, sa>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
+    sl::pixel_scales_kernel<<<grid, 256, 0, sa>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, c->d_isc.as<double2>(),
                                                   c->d_csc.as<double2>());
-    sl::table_colscale_kernel<<<dim3(sl::GCOLS, (unsigned)ch.nq), 128, 0, st>>>(
-        in.desc, ch.q0, in.M, k, c->d_csc.as<double2>(), c->d_tau.as<double>(), c->d_colscale.as<double>());
-    sl::table_slices_kernel<<<dim3((unsigned)(2 * ch.max_nks), (unsigned)ch.nq), sl::GCOLS, 0, st>>>(
-        in.desc, in.sq, ch.q0, in.M, k, c->d_csc.as<double2>(), c->d_tau.as<double>(), Bt);
+    sl::table_colscale_kernel<<<dim3(sl::GCOLS, (unsigned)ch.nq), 128, 0, sa>>>(
+        in.desc, ch.q0, in.M, k, c->d_csc.as<double2>(), set.tau.as<double>(), set.colscale.as<double>());
+    sl::table_slices_kernel<<<dim3((unsigned)(2 * ch.max_nks), (unsigned)ch.nq), sl::GCOLS, 0, sa>>>(
+        in.desc, in.sq, ch.q0, in.M, k, c->d_csc.as<double2>(), set.tau.as<double>(), Bt);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[1], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[1], sa));
   const int nch = 2 * ch.max_nks;
   const int nseg = std::min(dla::K1S_NSEG_MAX, std::max(dla::K1S_NSEG_MIN, (nch + 19) / 20));
   {
     const int cmax = (nch + nseg - 1) / nseg;   // 16-pixel chunks per segment
-    const int lam_cap = 16 * cmax + 8, px_cap = 16 * cmax;
-    const size_t smem = (size_t)lam_cap * 8 + (size_t)px_cap * 48 + (size_t)2 * sl::NSL * 3 * sl::K1Q_THREADS * 4;
+    const int lam_cap = 16 * cmax + 8;
+    const size_t smem = (size_t)lam_cap * 8 + (size_t)2 * sl::NSL * 3 * sl::K1Q_THREADS * 4;
     if (smem > 100 * 1024) BAD_ARG(c, "a quasar has too many pixels for the Voigt kernel's shared-memory staging");
-    sl::voigt_slices_lane_kernel<<<(unsigned)((int64_t)ch.nq * 2 * nsb * nseg), sl::K1Q_THREADS, smem, st>>>(
+    sl::voigt_slices_lane_kernel<<<(unsigned)((int64_t)ch.nq * nsb * nseg), sl::K1Q_THREADS, smem, sa>>>(
         in.desc, in.sq, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_isc.as<double2>(), c->d_etab256.as<double>(),
-        Aw, Au, aux, lam_cap, px_cap, nseg);
+        Aw, Au, aux, lam_cap, nseg);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[2], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[2], sa));
+  if (ov) {
+    CU_TRY(c, cudaEventRecord(set.planes_ready, sa));
+    CU_TRY(c, cudaStreamWaitEvent(sb, set.planes_ready, 0));
+  }
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[3], sb));
   {
     const int64_t ntiles = (int64_t)ch.nq * nsb * sl::UNITS;
     const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
-    if (c->k2s_mode == 1)
-      sl::contract_slices_tiles_kernel<1><<<grid, sl::THREADS, sl::K2S_SMEM, st>>>(in.sq, ch.q0, ch.nq, nsb, Aw, Au, Bt,
-                                                                                  c->d_colscale.as<double>(), G);
-    else if (c->k2s_mode == 2)
-      sl::contract_slices_tiles_kernel<2><<<grid, sl::THREADS, sl::K2S_SMEM, st>>>(in.sq, ch.q0, ch.nq, nsb, Aw, Au, Bt,
-                                                                                  c->d_colscale.as<double>(), G);
-    else
-      sl::contract_slices_tiles_kernel<0><<<grid, sl::THREADS, sl::K2S_SMEM, st>>>(in.sq, ch.q0, ch.nq, nsb, Aw, Au, Bt,
-                                                                                  c->d_colscale.as<double>(), G);
+    launch_k2s(c->k2s_mode, ov ? 3 : c->k2s_stages, grid, sb, in.sq, ch.q0, ch.nq, nsb, (const int8_t*)Aw, (const int8_t*)Au,
+               (const int8_t*)Bt, (const double*)set.colscale.as<double>(), G);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[3], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[4], sb));
   {
     dim3 grid((unsigned)(nsb * (sl::SB / sl::K2C_ROWS)), (unsigned)ch.nq);
-    sl::chol_rows_kernel<<<grid, sl::K2C_ROWS * 4, sl::K2C_SMEM, st>>>(in.desc, ch.q0, nsb, S, G, aux, d_perm, sample_ll_chunk,
+    sl::chol_rows_kernel<<<grid, sl::K2C_ROWS * 4, sl::K2C_SMEM, sb>>>(in.desc, ch.q0, nsb, S, G, aux, d_perm, sample_ll_chunk,
                                                                       ll_no, k, nseg);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[4], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[5], sb));
   if (S > 0 && ll_dla) {
-    dla::reduce_kernel<<<(unsigned)ch.nq, 256, 0, st>>>(in.desc, ch.q0, S, sample_ll_chunk, ll_no, ll_dla, lp_no,
+    dla::reduce_kernel<<<(unsigned)ch.nq, 256, 0, sb>>>(in.desc, ch.q0, S, sample_ll_chunk, ll_no, ll_dla, lp_no,
                                                          lp_dla, post, map_index);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[5], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[6], sb));
+  if (ov) {
+    CU_TRY(c, cudaEventRecord(set.done, sb));
+    set.busy = true;
+  }
   CU_TRY(c, cudaGetLastError());
   c->timing.launches += (S > 0 && ll_dla) ? 8 : 7;
   c->timing.contraction = 1;
@@ -293,6 +327,11 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
   double* B = c->d_bmat.as<double>();
   double* aux = c->d_aux.as<double>();
   cudaStream_t st = c->stream;
+  for (auto& set : c->sset)   // overlapped slice chunks still in flight share the per-chunk output buffers
+    if (set.busy) {
+      CU_TRY(c, cudaStreamWaitEvent(st, set.done, 0));
+      set.busy = false;
+    }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[0], st));
   {
     dim3 grid((unsigned)(((int64_t)(ch.max_npad / 4) * gen.ncol + 255) / 256), (unsigned)ch.nq);
@@ -341,6 +380,7 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
         num_lines, raw_stride);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[2], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[3], st));
   if (fused) {
     const int64_t ntiles = (int64_t)ch.nq * nsb;
     const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
@@ -370,13 +410,13 @@ static int launch_chunk(dla_ctx* c, const Inputs& in, const Chunk& ch, int64_t S
     dla::contract_chol_kernel<<<(unsigned)((int64_t)ch.nq * nsb), dla::K2_THREADS, smem, st>>>(
         in.desc, ch.q0, nsb, S, W, U, B, aux, d_perm, sample_ll_chunk, ll_no, k, nseg);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[3], st));
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[4], st));  // the Cholesky is part of the contraction kernels on this path
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[4], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[5], st));  // the Cholesky is part of the contraction kernels on this path
   if (S > 0 && ll_dla) {
     dla::reduce_kernel<<<(unsigned)ch.nq, 256, 0, st>>>(in.desc, ch.q0, S, sample_ll_chunk, ll_no, ll_dla, lp_no,
                                                          lp_dla, post, map_index);
   }
-  if (time_it) CU_TRY(c, cudaEventRecord(tev[5], st));
+  if (time_it) CU_TRY(c, cudaEventRecord(tev[6], st));
   CU_TRY(c, cudaGetLastError());
   c->timing.launches += ((S > 0 && ll_dla) ? 5 : 4) + (gen.generic ? 1 : 0);
   return DLA_OK;
@@ -389,11 +429,23 @@ static int collect_timing(dla_ctx* c, size_t nchunks) {
     float ms;
     CU_TRY(c, cudaEventElapsedTime(&ms, e[0], e[1])); c->timing.ms_phi += ms;
     CU_TRY(c, cudaEventElapsedTime(&ms, e[1], e[2])); c->timing.ms_voigt += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, e[2], e[3])); c->timing.ms_contract += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, e[3], e[4])); c->timing.ms_chol += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, e[4], e[5])); c->timing.ms_reduce += ms;
-    CU_TRY(c, cudaEventElapsedTime(&ms, e[0], e[5])); c->timing.ms_total += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[3], e[4])); c->timing.ms_contract += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[4], e[5])); c->timing.ms_chol += ms;
+    CU_TRY(c, cudaEventElapsedTime(&ms, e[5], e[6])); c->timing.ms_reduce += ms;
+    // chunks may overlap in time (contraction of chunk i under the Voigt kernel of chunk i + 1): the total is the
+    // span from the first chunk's start to the last completion, not a sum
+    CU_TRY(c, cudaEventElapsedTime(&ms, c->ev_time[0], e[6]));
+    c->timing.ms_total = std::max(c->timing.ms_total, (double)ms);
   }
+  return DLA_OK;
+}
+
+// both compute streams idle; the slice sets are free again
+static int sync_compute(dla_ctx* c) {
+  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  CU_TRY(c, cudaStreamSynchronize(c->stream2));
+  for (auto& set : c->sset) set.busy = false;
+  c->slice_chunks = 0;
   return DLA_OK;
 }
 
@@ -414,16 +466,22 @@ static int ensure_events(dla_ctx* c, size_t nchunks) {
 static int ensure_workspace(dla_ctx* c, int k, int64_t wu_doubles, int64_t bmat_doubles, int nq, int64_t S, bool need_ll_chunk,
                             int64_t a_bytes = 0, int64_t b_bytes = 0, int nq_slices = 0) {
   const int64_t S_pad = round_up(S + 1, dla::TS), S_pad128 = round_up(S + 1, dla::sl::SB);
-  CU_TRY(c, c->d_W.ensure((size_t)std::max<int64_t>(wu_doubles * 8, a_bytes)));
-  CU_TRY(c, c->d_U.ensure((size_t)std::max<int64_t>(wu_doubles * 8, a_bytes)));
+  CU_TRY(c, c->d_W.ensure((size_t)wu_doubles * 8));
+  CU_TRY(c, c->d_U.ensure((size_t)wu_doubles * 8));
   const ColGeom gen = col_geom(k);
   CU_TRY(c, c->d_bmat.ensure((size_t)(bmat_doubles / dla::NCOL + 1) * gen.ncol * 8));
   CU_TRY(c, c->d_aux.ensure((size_t)nq * 2 * dla::K1S_NSEG_MAX * S_pad128 * 8));
   if (nq_slices > 0) {
-    CU_TRY(c, c->d_btab.ensure((size_t)std::max<int64_t>(b_bytes, 32)));
     CU_TRY(c, c->d_G.ensure((size_t)nq_slices * S_pad128 * dla::sl::GCOLS * 8));
-    CU_TRY(c, c->d_tau.ensure((size_t)nq_slices * dla::sl::GCOLS * 8));
-    CU_TRY(c, c->d_colscale.ensure((size_t)nq_slices * dla::sl::GCOLS * 8));
+    for (int i = 0; i < (c->overlap ? 2 : 1); ++i) {
+      dla_ctx::SliceSet& set = c->sset[i];
+      CU_TRY(c, set.W.ensure((size_t)std::max<int64_t>(a_bytes, 32)));
+      CU_TRY(c, set.U.ensure((size_t)std::max<int64_t>(a_bytes, 32)));
+      CU_TRY(c, set.btab.ensure((size_t)std::max<int64_t>(b_bytes, 32)));
+      CU_TRY(c, set.tau.ensure((size_t)nq_slices * dla::sl::GCOLS * 8));
+      CU_TRY(c, set.colscale.ensure((size_t)nq_slices * dla::sl::GCOLS * 8));
+      CU_TRY(c, set.aux.ensure((size_t)nq_slices * 2 * dla::K1S_NSEG_MAX * S_pad128 * 8));
+    }
   }
   if (gen.generic) CU_TRY(c, c->d_G.ensure((size_t)nq * S_pad * gen.ncol * 8));
   if (need_ll_chunk) CU_TRY(c, c->d_ll_chunk.ensure((size_t)std::max<int64_t>(1, (int64_t)nq * S) * 8));
@@ -501,6 +559,16 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
   CREATE_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CREATE_TRY(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
   CREATE_TRY(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+  {
+    int prio_lo = 0, prio_hi = 0;
+    CREATE_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    // the persistent contraction must get its one CTA per SM as soon as a Voigt CTA of the next chunk retires
+    CREATE_TRY(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prio_hi));
+    for (auto& set : c->sset) {
+      CREATE_TRY(cudaEventCreateWithFlags(&set.planes_ready, cudaEventDisableTiming));
+      CREATE_TRY(cudaEventCreateWithFlags(&set.done, cudaEventDisableTiming));
+    }
+  }
   for (auto& ev : c->ev) CREATE_TRY(cudaEventCreate(&ev));
   // per-line constants, computed as libcerf's voigt() does: (x + i gamma)/sqrt(2)/sigma, /sqrt(2 pi)/sigma
   {
@@ -579,13 +647,37 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     c->use_slices = !(ct && strcmp(ct, "dmma") == 0) && !c->use_fused && !c->force_tile_k2 && !c->k2_rowsplit;
     const char* km = getenv("DLA_B200_K2S_MODE");
     c->k2s_mode = km ? atoi(km) : 0;
+    const char* ks = getenv("DLA_B200_K2S_STAGES");
+    c->k2s_stages = (ks && atoi(ks) == 3) ? 3 : 5;
+    const char* ov = getenv("DLA_B200_OVERLAP");
+    c->overlap = !(ov && strcmp(ov, "0") == 0);
+    const char* tp = getenv("DLA_B200_TRACE");
+    if (tp && *tp) {
+      c->trace_path = tp;
+      CREATE_TRY(c->d_trace.ensure((size_t)dla::sl::TRACE_CAP * 32));
+      unsigned long long* tptr = c->d_trace.as<unsigned long long>();
+      CREATE_TRY(cudaMemcpyToSymbol(dla::sl::g_trace, &tptr, sizeof tptr));
+    }
+    const char* oc = getenv("DLA_B200_OVERLAP_CHUNKS");
+    if (oc && atoi(oc) > 0) c->overlap_chunks = atoi(oc);
     const char* k1 = getenv("DLA_B200_K1");
     c->force_pixel_lane_k1 = k1 && strcmp(k1, "pixel") == 0;
     if (c->force_pixel_lane_k1) c->use_slices = false;
   }
-  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2S_SMEM));
-  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2S_SMEM));
-  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2S_SMEM));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<0, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(5)));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<0, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(3)));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<1, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(5)));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<2, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(5)));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<1, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(3)));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(3)));
+  // the contraction of one chunk and the Voigt kernel of the next share SMs: both ask for the largest shared-memory
+  // carveout, otherwise the SM is configured for the first one alone (132 KB for the 3-stage contraction) and the other
+  // kernel's CTAs wait for it to drain
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<0, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<1, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<2, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::chol_rows_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::chol_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2C_SMEM));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -618,11 +710,12 @@ void dla_destroy(dla_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  if (c->stream2) cudaStreamSynchronize(c->stream2);
   for (DevBuf* b : {&c->d_offset, &c->d_nhi, &c->d_perm, &c->d_etab256, &c->d_desc, &c->d_padded, &c->d_pidx, &c->d_flux, &c->d_mu, &c->d_om,
                     &c->d_nv, &c->d_M, &c->d_pix4, &c->d_sample_ll, &c->d_ll_no, &c->d_ll_dla, &c->d_lp_no, &c->d_lp_dla,
                     &c->d_post, &c->d_map, &c->d_W, &c->d_U, &c->d_bmat, &c->d_aux, &c->d_ll_chunk, &c->d_G, &c->d_krank,
                     &c->d_mrest, &c->d_mmu, &c->d_mM, &c->d_mlo, &c->d_lamk, &c->d_zq,
-                    &c->d_sq, &c->d_isc, &c->d_csc, &c->d_btab, &c->d_tau, &c->d_colscale,
+                    &c->d_sq, &c->d_isc, &c->d_csc, &c->d_trace,
                     &c->t_y, &c->t_l, &c->t_nv, &c->t_x, &c->t_om2, &c->t_aux, &c->t_E, &c->t_fq, &c->t_beta, &c->t_P,
                     &c->t_A1, &c->t_S, &c->t_gp, &c->t_g, &c->t_gsc, &c->t_desc})
     b->release();
@@ -630,6 +723,12 @@ void dla_destroy(dla_ctx* c) {
     if (ev) cudaEventDestroy(ev);
   for (auto& st : c->sstage)
     for (PinBuf* b : {&st.lamk, &st.fk, &st.nk, &st.padded, &st.pidx}) b->release();
+  for (auto& set : c->sset) {
+    for (DevBuf* b : {&set.W, &set.U, &set.btab, &set.tau, &set.colscale, &set.aux}) b->release();
+    if (set.planes_ready) cudaEventDestroy(set.planes_ready);
+    if (set.done) cudaEventDestroy(set.done);
+  }
+  if (c->stream2) cudaStreamDestroy(c->stream2);
   for (auto& ev : c->ev_time) cudaEventDestroy(ev);
   for (auto& ev : c->ev_sync) cudaEventDestroy(ev);
   if (c->s_in) cudaStreamDestroy(c->s_in);
@@ -727,8 +826,10 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
   auto quasar_bytes = [&](const QuasarDesc& d, long double gq) -> long double {
     long double b = 16.0L * S_pad * d.npad + gq;
     if (slices_elig) {
-      const long double a2 = 2.0L * nsb128 * nks_of(d) * sl::A_STEP7;
-      b = std::max(b, a2) + 8.0L * S_pad128 * sl::GCOLS + (long double)nks_of(d) * sl::B_QSTEP;
+      // sample planes of W and U + table planes + partial sums, once per set; G once
+      const long double per_set = 2.0L * nsb128 * nks_of(d) * sl::A_STEP7 + (long double)nks_of(d) * sl::B_QSTEP +
+                                  16.0L * dla::K1S_NSEG_MAX * S_pad128;
+      b = std::max(b, (c->overlap ? 2 : 1) * per_set + 8.0L * S_pad128 * sl::GCOLS);
     }
     return b;
   };
@@ -737,7 +838,10 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
     const long double gq = col_geom(c->p.k).generic ? 8.0L * S_pad * col_geom(c->p.k).ncol : 0.0L;  // G rows
     for (int64_t q = 0; q < Q; ++q) total += quasar_bytes(c->h_desc[(size_t)q], gq);
     const int64_t budget = c->p.workspace_bytes;
-    const int64_t pipe = std::min<int64_t>(max_pipe_chunks, Q / 8);
+    int64_t pipe = std::min<int64_t>(max_pipe_chunks, Q / 8);
+    // overlapped slice path: the contraction of chunk i runs under the Voigt kernel of chunk i + 1, so a batch wants
+    // many chunks (the first Voigt and the last contraction run alone) of at least a few quasars each
+    if (slices_elig && c->overlap) pipe = std::max<int64_t>(pipe, std::min<int64_t>(c->overlap_chunks, Q / 6));
     const int64_t nch = std::max<int64_t>(std::max<int64_t>(1, pipe), (int64_t)ceill(total / budget));
     const long double target = total / nch;
     // quasar-count cap of a chunk: the persistent contraction runs nq * nsb tiles in waves of num_sms; among the
@@ -783,8 +887,8 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
         ++ch.nq;
         ++q;
       }
-      // int32 accumulators hold 7 * 2^14 * pixels: far beyond any spectrum of the pipeline, checked all the same
-      ch.slices = slices_elig && ch.all_ident && ch.max_nks * sl::KS <= 16384;
+      // int32 accumulators hold 7 * 2^15 * pixels: far beyond any spectrum of the pipeline, checked all the same
+      ch.slices = slices_elig && ch.all_ident && ch.max_nks * sl::KS <= 8192;
       c->chunks.push_back(ch);
     }
   }
@@ -818,10 +922,11 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
     int64_t wu = 0, bm = 0, ab = 0, bb = 0;
     int nq = 0, nqs = 0;
     for (const Chunk& ch : c->chunks) {
-      wu = std::max(wu, ch.wu_doubles);
-      bm = std::max(bm, ch.bmat_doubles);
       nq = std::max(nq, ch.nq);
-      if (ch.slices) {
+      if (!ch.slices) {
+        wu = std::max(wu, ch.wu_doubles);
+        bm = std::max(bm, ch.bmat_doubles);
+      } else {
         ab = std::max(ab, ch.a_bytes);
         bb = std::max(bb, ch.b_bytes);
         nqs = std::max(nqs, ch.nq);
@@ -896,7 +1001,7 @@ static int run_chunk(dla_ctx* c, size_t i) {
                         c->d_lp_no.as<double>(), c->d_lp_dla.as<double>(), c->d_post.as<double>(),
                         c->d_map.as<int32_t>(), &c->ev_time[NTEV * i]);
   if (rc != DLA_OK) return rc;
-  CU_TRY(c, cudaEventRecord(c->ev_sync[2 * i + 1], c->stream));
+  CU_TRY(c, cudaEventRecord(c->ev_sync[2 * i + 1], (ch.slices && c->overlap) ? c->stream2 : c->stream));
   c->timing.chunks++;
   return DLA_OK;
 }
@@ -941,8 +1046,21 @@ int dla_run_staged(dla_ctx* c) {
     int rc = run_chunk(c, i);
     if (rc != DLA_OK) return rc;
   }
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
-  int rc = collect_timing(c, c->chunks.size());
+  int rc = sync_compute(c);
+  if (rc != DLA_OK) return rc;
+  if (!c->trace_path.empty()) {   // the trace of the LAST run (the counter restarts with every run)
+    unsigned int n = 0, zero = 0;
+    CU_TRY(c, cudaMemcpyFromSymbol(&n, dla::sl::g_trace_n, sizeof n));
+    CU_TRY(c, cudaMemcpyToSymbol(dla::sl::g_trace_n, &zero, sizeof zero));
+    n = std::min(n, dla::sl::TRACE_CAP);
+    std::vector<unsigned long long> h((size_t)n * 4);
+    if (n) CU_TRY(c, cudaMemcpy(h.data(), c->d_trace.p, (size_t)n * 32, cudaMemcpyDeviceToHost));
+    if (FILE* f = fopen(c->trace_path.c_str(), "wb")) {
+      fwrite(h.data(), 8, h.size(), f);
+      fclose(f);
+    }
+  }
+  rc = collect_timing(c, c->chunks.size());
   if (rc != DLA_OK) return rc;
   c->ran = true;
   return DLA_OK;
@@ -1018,7 +1136,7 @@ static int run_pipelined(dla_ctx* c, double* sample_ll, double* ll_no_dla, doubl
   rc = download_small(c, c->s_out, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
   if (rc != DLA_OK) return rc;
   CU_TRY(c, cudaStreamSynchronize(c->s_in));
-  CU_TRY(c, cudaStreamSynchronize(c->stream));
+  if ((rc = sync_compute(c)) != DLA_OK) return rc;
   CU_TRY(c, cudaStreamSynchronize(c->s_out));
   c->hin = {};
   float ms;

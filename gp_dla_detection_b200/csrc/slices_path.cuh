@@ -14,10 +14,12 @@
 //   chol_rows_kernel         per-sample bordered 21 x 21 Cholesky (registers, one quad per sample)  (K2c)
 //
 // Fixed point.  Sample side: t = w / c_w in [0, 1) or t = u / c_u in (-1/2, 1/2) enters a double's mantissa by ONE
-// fma with a magic constant (1.0 / 1.5): X = round(t 2^52).  X = sum_i a_i 256^(6-i) in balanced digits a_i in
-// [-128, 127], so t = sum_i a_i 2^(-8 i - 4).  Table side: b = entry / tau in [-1, 1] with 54 fractional bits,
+// fma with a magic constant (1.0 / 1.5): X = round(t 2^52), two's complement.  Its bytes ARE the slices: X = a_0 256^6
+// + sum_{i>=1} a_i 256^(6-i) with a_0 the signed top byte and a_1..a_6 plain unsigned bytes (the MMAs of slice 0 declare
+// a signed A operand, the others an unsigned one), so t = sum_i a_i 2^(-8 i - 4) with no digit arithmetic at all.
+// Table side: b = entry / tau in [-1, 1] with 54 fractional bits in balanced digits b_j in [-128, 127],
 // b = sum_j b_j 2^(-8 j - 6).  Slice products with i + j = d share the weight 2^(-8 d - 10) and accumulate exactly
-// in int32 (|sum| <= 7 * 2^14 * pixels < 2^31 for pixels <= 18 000); pairs with i + j >= 7 are dropped.
+// in int32 (|sum| <= 7 * 2^15 * pixels < 2^31 for pixels <= 9 000); pairs with i + j >= 7 are dropped.
 #ifndef GPDLA_SLICES_PATH_CUH
 #define GPDLA_SLICES_PATH_CUH
 
@@ -34,10 +36,31 @@ constexpr int B_QSTEP = 3 * B_STEP64 + 2 * B_STEP32;   // table bytes per K step
 constexpr int GCOLS = 256;                     // row of G: [0, 224) W.Phi (k (k+1) / 2 used), [224, 256) U.M (k used)
 constexpr int VOFF_S = 224;
 constexpr int UNITS = 5;                       // column units per sample block: 64, 64, 64, 32 (W planes), 32 (U planes)
-constexpr int K2S_STAGES = 5;
 constexpr int K2S_STAGE = A_STEP7 + B_STEP64;  // 43 008
-constexpr size_t K2S_SMEM = (size_t)K2S_STAGES * K2S_STAGE + 1024 + 256;
-constexpr int K1Q_THREADS = 64;                // one CTA = 64 hypotheses (half a sample block) x one spectrum segment
+// ring depth of the contraction: 5 when it has the SM to itself, 3 (130 KB) when Voigt CTAs of the next chunk share it
+constexpr size_t k2s_smem(int stages) { return (size_t)stages * K2S_STAGE + 1024 + 256; }
+constexpr int K1Q_THREADS = 128;               // one CTA = the 128 hypotheses of a sample block x one spectrum segment
+
+// CTA residency trace (diagnosis, DLA_B200_TRACE=<file>): {kernel id, SM id, start ns, end ns} per CTA
+__device__ unsigned long long* g_trace = nullptr;
+__device__ unsigned int g_trace_n = 0;
+constexpr unsigned int TRACE_CAP = 1u << 20;
+__device__ __forceinline__ unsigned long long trace_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void trace_put(unsigned long long kernel_id, unsigned long long t0) {
+  unsigned int smid;
+  asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+  const unsigned int i = atomicAdd(&g_trace_n, 1u);
+  if (i < TRACE_CAP) {
+    g_trace[4 * (size_t)i] = kernel_id;
+    g_trace[4 * (size_t)i + 1] = smid;
+    g_trace[4 * (size_t)i + 2] = t0;
+    g_trace[4 * (size_t)i + 3] = trace_now();
+  }
+}
 
 // per quasar of the staged batch (device array parallel to QuasarDesc)
 struct SliceQuasar {
@@ -136,8 +159,10 @@ __global__ void table_colscale_kernel(const QuasarDesc* __restrict__ desc, int q
     colscale[(int64_t)blockIdx.y * GCOLS + c] = t * 0.0009765625;
   }
 }
-// planes: unit u < 3: [K step][slice][2][64 columns][16 B] at b_off + u nks B_STEP64; u = 3, 4: 32 columns, at
-// b_off + 3 nks B_STEP64 + (u - 3) nks B_STEP32.  One thread per (column, 16-pixel chunk); pixels >= n are zero.
+// planes: unit u < 3: [K step][2][slice][64 columns][16 B] at b_off + u nks B_STEP64; u = 3, 4: 32 columns, at
+// b_off + 3 nks B_STEP64 + (u - 3) nks B_STEP32.  Within a 16-byte K chunk the slices are stacked like extra columns
+// (row j N + c of the operand = slice j, column c), so that ONE MMA multiplies a sample slice with several table
+// slices at once.  One thread per (column, 16-pixel chunk); pixels >= n are zero.
 __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar* __restrict__ sq, int q0,
                                     const double* __restrict__ M, int k, const double2* __restrict__ csc,
                                     const double* __restrict__ tau, int8_t* __restrict__ planes) {
@@ -165,7 +190,7 @@ __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const S
   const int cc = (u < 3) ? (col & 63) : (col & 31);
   const int64_t ubase = (u < 3) ? (int64_t)u * s.nks * B_STEP64 : (int64_t)3 * s.nks * B_STEP64 + (int64_t)(u - 3) * s.nks * B_STEP32;
   const int ks = ch >> 1, c2 = ch & 1;
-  int8_t* base = planes + s.b_off + ubase + (int64_t)ks * (NSL * 2 * N * 16) + (int64_t)c2 * (N * 16) + cc * 16;
+  int8_t* base = planes + s.b_off + ubase + (int64_t)ks * (NSL * 2 * N * 16) + (int64_t)c2 * (NSL * N * 16) + cc * 16;
 #pragma unroll
   for (int sl_ = 0; sl_ < NSL; ++sl_) {
     uint32_t w[4];
@@ -176,7 +201,7 @@ __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const S
       for (int b = 0; b < 4; ++b) v |= (uint32_t)((dig[4 * q + b] >> (8 * (NSL - 1 - sl_))) & 0xffu) << (8 * b);
       w[q] = v;
     }
-    *reinterpret_cast<uint4*>(base + (int64_t)sl_ * (2 * N * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
+    *reinterpret_cast<uint4*>(base + (int64_t)sl_ * (N * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
   }
 }
 
@@ -189,17 +214,14 @@ __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const S
 //   planes: a_off + ((sb * nks + ks) * 7 + slice) * 4096 + (chunk & 1) * 2048 + row * 16
 // ------------------------------------------------------------------------------------------------------------
 // m[h] = fma(value, 1 / scale, MAGIC): bits(m) - bits(MAGIC) = X = round(t 2^52) (two's complement, |X| < 2^52);
-// digits of X, slice i = byte 6 - i; out[i] = the four pixels' slice-i bytes
+// slice i = byte 6 - i of X; out[i] = the four pixels' slice-i bytes.  Only the high word needs the subtraction.
 template <uint32_t MAGIC_HI>
 __device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NSL]) {
-  constexpr uint64_t C = 0x0000808080808080ull;
-  constexpr uint64_t K = C - ((uint64_t)MAGIC_HI << 32);
   uint32_t lo[4], hi[4];
 #pragma unroll
   for (int h = 0; h < 4; ++h) {
-    const uint64_t b = ((uint64_t)__double_as_longlong(m[h]) + K) ^ C;
-    lo[h] = (uint32_t)b;
-    hi[h] = (uint32_t)(b >> 32);
+    lo[h] = (uint32_t)__double2loint(m[h]);
+    hi[h] = (uint32_t)__double2hiint(m[h]) - MAGIC_HI;
   }
   const uint32_t t0 = __byte_perm(lo[0], lo[1], 0x5140), t1 = __byte_perm(lo[2], lo[3], 0x5140);
   const uint32_t t2 = __byte_perm(lo[0], lo[1], 0x7362), t3 = __byte_perm(lo[2], lo[3], 0x7362);
@@ -215,20 +237,21 @@ __device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NS
 }
 
 #ifndef DLA_K1Q_MINB
-#define DLA_K1Q_MINB 6   // resident CTAs per SM (6 -> 168 registers)
+#define DLA_K1Q_MINB 4   // resident CTAs per SM (4 x 128 threads -> 128 registers)
 #endif
 __global__ void __launch_bounds__(K1Q_THREADS, DLA_K1Q_MINB)
 voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar* __restrict__ sq, int q0, int nsb /* 128-sample blocks */,
                          int64_t S, const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
                          const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
                          const double2* __restrict__ isc, const double* __restrict__ etab256, int8_t* __restrict__ Wplanes,
-                         int8_t* __restrict__ Uplanes, double* __restrict__ aux, int lam_cap, int px_cap, int nseg) {
+                         int8_t* __restrict__ Uplanes, double* __restrict__ aux, int lam_cap, int nseg) {
   extern __shared__ __align__(16) double k1q_smem[];
   __shared__ double etab_s[256];
-  const int nsb64 = 2 * nsb;
+  const bool tracing = g_trace != nullptr;
+  const unsigned long long trace_t0 = (tracing && threadIdx.x == 0) ? trace_now() : 0ull;
   const int seg = blockIdx.x % nseg;
   const int tile = blockIdx.x / nseg;
-  const int ql = tile / nsb64, sb64 = tile % nsb64;
+  const int ql = tile / nsb, sb = tile % nsb;
   const QuasarDesc d = desc[q0 + ql];
   const SliceQuasar sqq = sq[q0 + ql];
   const int tid = threadIdx.x;
@@ -239,21 +262,17 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
   const int lbase = max(4 * g0 - 2, 0), llast = min(4 * g1 + 5, Pm1);
   const int j0 = min(4 * g0, n), j1 = min(4 * g1, n);                     // kept pixels this segment emits
   const int nsteps = (g1 > g0) ? g1 - g0 + 2 : 0;
+  // shared: the segment's wavelengths and the piece staging only; the per-pixel records are warp-uniform global loads
+  // (L1 hits), which keeps a CTA at 26 KB so that three of them fit on an SM beside the contraction of the previous chunk
   double* lam_s = k1q_smem;
-  double2* px_s = reinterpret_cast<double2*>(k1q_smem + lam_cap);
-  double2* sc_s = px_s + 2 * px_cap;
-  uint32_t* stg_s = reinterpret_cast<uint32_t*>(sc_s + px_cap) + tid;   // [14 pieces][3 steps][64 lanes]
+  uint32_t* stg_s = reinterpret_cast<uint32_t*>(k1q_smem + lam_cap) + tid;   // [14 pieces][3 steps][128 lanes]
   for (int i = tid; i < 256; i += K1Q_THREADS) etab_s[i] = etab256[i];
   {
     const double* lam_g = padded_wavelengths + d.pad_off;
     for (int i = tid; i < 4 * nsteps; i += K1Q_THREADS) lam_s[i] = __ldg(lam_g + min(max(4 * g0 - 2 + i, lbase), llast));
-    const double2* px_g = pix4 + 2 * (d.pix_off + j0);
-    for (int i = tid; i < 2 * (j1 - j0); i += K1Q_THREADS) px_s[i] = __ldg(px_g + i);
-    const double2* sc_g = isc + d.pix_off + j0;
-    for (int i = tid; i < j1 - j0; i += K1Q_THREADS) sc_s[i] = __ldg(sc_g + i);
   }
   __syncthreads();
-  const int64_t s = (int64_t)sb64 * K1Q_THREADS + tid;
+  const int64_t s = (int64_t)sb * K1Q_THREADS + tid;
   const bool real = s < S;
   const double off = real ? offset_sorted[s] : 0.0;       // process_qsos.m:163-165, separately rounded
   const double N = real ? nhi_sorted[s] : 0.0;
@@ -267,13 +286,13 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
     nc1[j] = ncw[j] * g_lines.g1p[j];
     nc2[j] = ncw[j] * g_lines.gq[2];
   }
-  const double2* px = px_s - 2 * j0;   // indexed by 2 * kept pixel
-  const double2* sc = sc_s - j0;       // indexed by kept pixel
+  const double2* px = pix4 + 2 * d.pix_off;   // indexed by 2 * kept pixel
+  const double2* sc = isc + d.pix_off;        // indexed by kept pixel
   const int jdead = (j1 > j0) ? j0 : 0;  // a live pixel of this segment stands in for dead ones (values discarded)
   const int gfull = n >> 2;
   const int64_t S_pad = (int64_t)nsb * SB;
-  const int row = (sb64 & 1) * K1Q_THREADS + tid;
-  const int64_t sb_base = sqq.a_off + (int64_t)(sb64 >> 1) * sqq.nks * A_STEP7 + row * 16;
+  const int row = tid;
+  const int64_t sb_base = sqq.a_off + (int64_t)sb * sqq.nks * A_STEP7 + row * 16;
   int8_t* wq = Wplanes + sb_base;
   int8_t* uq = Uplanes + sb_base;
 
@@ -307,7 +326,7 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
         const int j = 4 * g + h;
-        const double2 is = have_px ? sc[(j < n) ? j : jdead] : make_double2(0.0, 0.0);
+        const double2 is = have_px ? __ldg(sc + ((j < n) ? j : jdead)) : make_double2(0.0, 0.0);
         mw[h] = fma(w[h], is.x, 1.0);
         mu_[h] = fma(u[h], is.y, 1.5);
       }
@@ -339,6 +358,7 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
   double* auxq = aux + (int64_t)ql * 2 * nseg * S_pad;
   auxq[(int64_t)seg * S_pad + s] = q0acc;
   auxq[(int64_t)(nseg + seg) * S_pad + s] = ldacc;
+  if (tracing && threadIdx.x == 0) trace_put(1, trace_t0);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -369,8 +389,38 @@ __device__ __forceinline__ K2sTile k2s_decode(int t, const SliceQuasar* __restri
   return r;
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(THREADS, 1)
+// One K step of a tile: sample slice i meets the table slices 0 .. 6 - i in ONE wide MMA (two when that is more than
+// 256 columns): operand rows [0, (7 - i) N) of the stacked table planes, accumulators of the diagonals i .. 6.
+// 10 MMAs (N = 64) or 7 (N = 32) instead of 28: the sample slice is read from shared memory once per MMA, and the
+// single issuing thread is no longer the limit (a 128 x 64 x 32 MMA lasts 32 clocks, issuing one costs about 70).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+template <int N>
+__device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, uint32_t tmem_base, uint32_t first) {
+  constexpr uint64_t HI = (uint64_t)(((128u >> 4) & 0x3FFFu) | (1u << 14)) << 32;   // stride between 8-row groups, version 1
+  const uint32_t a_lo = ((abase >> 4) & 0x3FFFu) | ((uint32_t)((SB * 16) >> 4) << 16);
+  const uint32_t b_lo = ((bbase >> 4) & 0x3FFFu) | ((uint32_t)((NSL * 16 * N) >> 4) << 16);
+#pragma unroll
+  for (int i = 0; i < NSL; ++i) {
+    const uint64_t ad = HI | (uint64_t)(a_lo + (uint32_t)(i * ((2 * SB * 16) >> 4)));
+    const int ntot = (NSL - i) * N;
+#pragma unroll
+    for (int r0 = 0; r0 < ntot; r0 += 256) {
+      const int np = (ntot - r0 < 256) ? ntot - r0 : 256;
+      const uint64_t bd = HI | (uint64_t)(b_lo + (uint32_t)r0);   // r0 rows of 16 bytes
+      // A format (bits [7, 10)): 1 = signed 8 bit for the top slice, 0 = unsigned for the plain low bytes
+      umma_i8(tmem_base + (uint32_t)(i * N + r0), ad, bd, idesc_i8(SB, np) & ~((i == 0) ? 0u : (1u << 7)), (i == 0) ? first : 1u);
+    }
+  }
+}
+
+// launch bounds: the second number only caps the registers at 80 (shared memory allows one CTA per SM anyway), so that
+// three Voigt CTAs of the next chunk (128 registers x 128 threads each) fit beside this kernel on an SM
+template <int MODE, int K2S_STAGES>
+__global__ void __launch_bounds__(THREADS, 4)
 contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq, int nsb, const int8_t* __restrict__ Aw,
                              const int8_t* __restrict__ Au, const int8_t* __restrict__ Bt, const double* __restrict__ colscale,
                              double* __restrict__ G) {
@@ -383,6 +433,8 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ntiles = nq * nsb * UNITS;
+  const bool tracing = g_trace != nullptr;
+  const unsigned long long trace_t0 = (tracing && tid == 0) ? trace_now() : 0ull;
 
   if (tid == 0) {
     for (int s = 0; s < K2S_STAGES; ++s) {
@@ -426,31 +478,23 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
     uint32_t it = 0, tcount = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
       const K2sTile tl = k2s_decode(t, sq, q0, nsb, Aw, Au, Bt);
-      const uint32_t N = (uint32_t)tl.N;
-      const uint32_t idesc = idesc_i8(SB, tl.N);
       bar_wait(tempty, (tcount & 1) ^ 1);   // the epilogue has drained the previous tile's accumulators
       tc_fence_after();
       for (int ks = 0; ks < tl.nks; ++ks, ++it) {
         const int st = it % K2S_STAGES;
         bar_wait(&full[st], (it / K2S_STAGES) & 1);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t abase = s32(smem + (size_t)st * K2S_STAGE);
-          const uint32_t bbase = abase + A_STEP7;
-          const uint32_t first = (ks == 0) ? 0u : 1u;
+        // every lane forms the (warp-uniform) operands; one elected lane issues
+        const uint32_t abase = s32(smem + (size_t)st * K2S_STAGE);
+        const uint32_t first = (ks == 0) ? 0u : 1u;
+        const bool last = ks == tl.nks - 1;
+        if (elect_one()) {
           if (MODE != 1) {
-#pragma unroll
-            for (int i = 0; i < NSL; ++i) {
-              const uint64_t ad = smem_desc(abase + i * (2 * SB * 16), SB * 16, 128);
-#pragma unroll
-              for (int j = 0; j + i < NSL; ++j) {
-                const uint64_t bd = smem_desc(bbase + j * (2 * 16) * N, 16 * N, 128);
-                umma_i8(tmem_base + (uint32_t)(i + j) * N, ad, bd, idesc, (i == 0) ? first : 1u);
-              }
-            }
+            if (tl.N == 64) k2s_issue_step<64>(abase, abase + A_STEP7, tmem_base, first);
+            else k2s_issue_step<32>(abase, abase + A_STEP7, tmem_base, first);
           }
           umma_commit(&empty[st]);
-          if (ks == tl.nks - 1) umma_commit(tfull);
+          if (last) umma_commit(tfull);
         }
         __syncwarp();
       }
@@ -495,6 +539,7 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
   if (warp == 2) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
   }
+  if (tracing && tid == 0) trace_put(2, trace_t0);
 }
 
 // ------------------------------------------------------------------------------------------------------------

@@ -23,7 +23,7 @@ from tests.helpers import oracle_batch, prepared_config  # noqa: E402
 
 
 def run(env, prepared, samples, sp, k, S, reps):
-    for key in ("DLA_B200_CONTRACT", "DLA_B200_K2S_MODE"):
+    for key in ("DLA_B200_CONTRACT", "DLA_B200_K2S_MODE", "DLA_B200_OVERLAP", "DLA_B200_K2S_STAGES", "DLA_B200_OVERLAP_CHUNKS"):
         os.environ.pop(key, None)
     os.environ.update(env)
     with DlaContext(k=k, num_samples=S) as ctx:
@@ -49,14 +49,24 @@ def main():
     ap.add_argument("--config", default="config1")
     ap.add_argument("--modes", action="store_true")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--only-default", action="store_true", help="one context with the environment as it is (tracing)")
+    ap.add_argument("--variants", nargs="*", default=[], help="extra runs, each a comma list of ENV=value")
     a = ap.parse_args()
     params, model, samples, sp, prepared = prepared_config(a.config, a.quasars, a.samples, "reference")
     k = 20
     t0 = time.time()
     out_s, tm_s = run({}, prepared, samples, sp, k, a.samples, a.reps)
+    if a.only_default:
+        print(json.dumps({"path": "slices (overlapped chunks)", "timing": tm_s}), flush=True)
+        return
     out_d, tm_d = run({"DLA_B200_CONTRACT": "dmma"}, prepared, samples, sp, k, a.samples, a.reps)
-    print(json.dumps({"path": "slices", "timing": tm_s}), flush=True)
+    print(json.dumps({"path": "slices (overlapped chunks)", "timing": tm_s}), flush=True)
     print(json.dumps({"path": "dmma", "timing": tm_d}), flush=True)
+    for env in a.variants:
+        e = dict(kv.split("=") for kv in env.split(",") if kv)
+        o, tm = run(e, prepared, samples, sp, k, a.samples, a.reps)
+        same = bool(np.array_equal(o["sample_log_likelihoods_dla"], out_s["sample_log_likelihoods_dla"], equal_nan=True))
+        print(json.dumps({"path": "slices " + env, "bitwise_equal_to_default": same, "timing": tm}), flush=True)
     x, y = out_s["sample_log_likelihoods_dla"], out_d["sample_log_likelihoods_dla"]
     rel = np.abs(x - y) / np.abs(y)
     print(json.dumps({"compare": "slices vs dmma", "quasars": a.quasars, "nan_slices": int(np.isnan(x).sum()),
