@@ -4,9 +4,10 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-One step = one pass of the hot path (K0 Phi table, K1 Voigt+weights, K2 DMMA contraction +
-Cholesky, K3 log-mean-exp/argmax) over one batch of synthetic quasars of BASELINE.json
-config-2 shape (1217 pixels, k = 20, S = 10000 hypotheses).  Quasars shard across ranks with
+One step = one pass of the hot path (K0 tables, K1 Voigt+weights, K2 contraction + Cholesky, K3
+log-mean-exp/argmax) over one batch of synthetic quasars of BASELINE.json config-2 shape (1217
+pixels, k = 20, S = 10000 hypotheses).  For k <= 20 the contraction is the exact-slice int8 tcgen05
+kernel (DLA_B200_CONTRACT=dmma selects the FP64 DMMA kernels instead; k > 20 always uses them).  Quasars shard across ranks with
 no collective on the data path (weak scaling: --quasars per GPU per step).  Rank 0 prints ONE
 JSON line.  `value` is device-resident throughput (inputs already in HBM), `e2e` goes through
 dla_eval_batch with pinned HOST buffers (H2D + D2H inside the timed region).
@@ -31,6 +32,11 @@ N_PIX, K_RANK = 1217, 20
 # K2's DRAM traffic per quasar from the committed ncu --set full capture (3.2578 GB read + 0.0061 GB written
 # by one 16-quasar launch, profiles/r01_ncu_full_summary.txt); not measured inside bench.py
 NCU_K2_DRAM_GB_PER_QUASAR = (3.257835 + 0.006098) / 16
+# the same for the int8 slice contraction (profiles/r02_ncu_slices_summary.txt: 2.919 GB read + 0.325 GB written by one
+# 16-quasar launch) and the FP64 instructions of the slice-emitting Voigt kernel per (hypothesis, pixel)
+NCU_K2S_DRAM_GB_PER_QUASAR = (2.919130 + 0.325005) / 16
+NCU_K1S_FP64_PER_PIXEL = 60.0
+FP64_PIPE_TFLOPS = 37.1   # register-resident DMMA / DFMA loops, tools/probe_fp64.cu, profiles/r01_probe_fp64.jsonl
 # BASELINE.json configs as (rank, grid spacing, ragged masking, hypotheses); SURVEY.md 8(d)
 WORKLOADS = {
     "config2": {"k": 20, "dlambda": 0.25, "ragged": False, "samples": 10000, "pixels": 1217,
@@ -286,7 +292,7 @@ def run_ours(args):
     barrier()
     sampler.start()
     t0 = time.perf_counter()
-    ev_ms = {"ms_total": 0.0, "ms_phi": 0.0, "ms_voigt": 0.0, "ms_contract": 0.0, "ms_reduce": 0.0}
+    ev_ms = {"ms_total": 0.0, "ms_phi": 0.0, "ms_voigt": 0.0, "ms_contract": 0.0, "ms_chol": 0.0, "ms_reduce": 0.0}
     launches = 0
     for _ in range(args.steps):
         ctx.run_staged()
@@ -357,24 +363,75 @@ def run_ours(args):
     ach = flop_per_step / t_contract / 1e12
     k2_name = ("contract_chol_persistent_kernel (K2: persistent DMMA contraction + Cholesky epilogue)" if K_RANK <= 20 else
                "contract_block_kernel + chol_generic_kernel (K2 generic rank: column-block DMMA contraction, smem Cholesky)")
-    roofline = {"kernel": k2_name, "bound": "tensor",
-                "achieved": ach, "peak": dgemm_tflops, "unit": "TFLOP/s", "frac": ach / dgemm_tflops,
-                "traffic": (NCU_K2_DRAM_GB_PER_QUASAR * Q / max(1, tm["chunks"])) if args.workload == "config2" and S == 10000 else None,
-                "traffic_unit": "GB per launch (dram__bytes_read.sum + dram__bytes_write.sum of profiles/r01_ncu_full_summary.txt, "
-                                "scaled from its 16-quasar launch; algorithmic W+U bytes are 0.198 GB per quasar)",
-                "peak_source": "FP64 tensor peak = cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json "
-                               "has no FP64 figure; the profiling guide states no FP64 fallback)",
-                "algorithmic_flop_per_launch": flop_per_step / max(1, tm["chunks"]),
-                "launches_per_step": int(tm["chunks"]), "ms_per_step": 1e3 * t_contract,
-                "step_frac_end_to_end": (flop_per_step / (dev_s / args.steps) / 1e12) / dgemm_tflops}
-    wu_bytes = 16.0 * S * n_sum                                    # W and U written once (fp64)
-    roofline_voigt = {"kernel": "voigt_weights_lane_kernel (K1, sample-per-lane)", "bound": "fp64 vector pipe (reported vs hbm as north_star asks)",
-                      "achieved": wu_bytes / t_voigt / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                      "frac": wu_bytes / t_voigt / 1e9 / hbm_peak,
-                      "faddeeva_evals_per_s": 3.0 * S * float((batch.n_full + 6).sum()) / t_voigt,
-                      "ms_per_step": 1e3 * t_voigt,
-                      "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"}
-    dominant = "K1 voigt_weights_lane_kernel" if t_voigt > t_contract else "K2 " + k2_name.split(" ")[0]
+    slices = int(tm.get("contraction", 0)) == 1
+    step_tflops = flop_per_step / (dev_s / args.steps) / 1e12
+    if not slices:
+        roofline = {"kernel": k2_name, "bound": "tensor",
+                    "achieved": ach, "peak": dgemm_tflops, "unit": "TFLOP/s", "frac": ach / dgemm_tflops,
+                    "peak_pipe": FP64_PIPE_TFLOPS,
+                    "frac_of_pipe": ach / FP64_PIPE_TFLOPS,
+                    "traffic": (NCU_K2_DRAM_GB_PER_QUASAR * Q / max(1, tm["chunks"])) if args.workload == "config2" and S == 10000 else None,
+                    "traffic_unit": "GB per launch (dram__bytes_read.sum + dram__bytes_write.sum of profiles/r01_ncu_full_summary.txt, "
+                                    "scaled from its 16-quasar launch; algorithmic W+U bytes are 0.198 GB per quasar)",
+                    "peak_source": "FP64 tensor peak = cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 "
+                                   "figure); peak_pipe = register-resident DMMA loop of tools/probe_fp64.cu "
+                                   "(profiles/r01_probe_fp64.jsonl), a constant, not re-measured here",
+                    "algorithmic_flop_per_launch": flop_per_step / max(1, tm["chunks"]),
+                    "launches_per_step": int(tm["chunks"]), "ms_per_step": 1e3 * t_contract,
+                    "step_frac_end_to_end": step_tflops / dgemm_tflops}
+    else:
+        # int8 slice contraction: 28 slice pairs x (224 + 32) columns x n_pad32 pixels x S_pad128 samples, 2 ops per MAC;
+        # the tensor peak for 8-bit operands is twice the measured bf16 figure (same pipe, K = 32 instead of 16 per MMA)
+        spad = (S + 1 + 127) // 128 * 128
+        npad32 = float(((batch.n + 31) // 32 * 32).sum())
+        int8_ops = 2.0 * 28 * 256 * spad * npad32
+        bf16_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+        int8_peak = 2.0 * bf16_peak
+        ach8 = int8_ops / t_contract / 1e12
+        roofline = {"kernel": "contract_slices_tiles_kernel (K2s: exact-slice int8 tcgen05 contraction, 7 x 7 slices, "
+                              "int32 TMEM accumulators, fp64 recombination)",
+                    "bound": "tensor", "achieved": ach8, "peak": int8_peak, "unit": "TOP/s (int8)", "frac": ach8 / int8_peak,
+                    "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops_sustained (8-bit operands run at twice the bf16 rate on "
+                                    "the same pipe; tools/probe_umma.cu: 128 x 256 x 32 kind::i8 MMAs issue at exactly that rate)"
+                                    if peaks else "2 x fallback 1400 TFLOP/s bf16 sustained"),
+                    "algorithmic_int8_op_per_launch": int8_ops / max(1, tm["chunks"]),
+                    "fp64_equivalent": {"achieved_tflops": ach, "dgemm_peak_tflops": dgemm_tflops, "ratio": ach / dgemm_tflops,
+                                        "note": "n k (k+3) fp64 flops per (quasar, hypothesis) (SURVEY 8d) / K2s time, against the "
+                                                "cuBLAS DGEMM 8192^3 measured in this run: the contraction no longer runs on the FP64 pipe"},
+                    "traffic": (NCU_K2S_DRAM_GB_PER_QUASAR * Q / max(1, tm["chunks"])) if args.workload == "config2" and S == 10000 else None,
+                    "traffic_unit": "GB per launch (dram__bytes_read.sum + dram__bytes_write.sum of profiles/r02_ncu_slices_summary.txt, "
+                                    "scaled from its 16-quasar launch; algorithmic bytes: int8 planes of W and U 0.177 GB + G 0.021 GB per quasar)",
+                    "launches_per_step": int(tm["chunks"]), "ms_per_step": 1e3 * t_contract,
+                    "step_fp64_equivalent_vs_dgemm": step_tflops / dgemm_tflops}
+    if slices:
+        # K1s is bound by the FP64 vector pipe: FP64 instructions per (hypothesis, pixel) from the ncu capture of the same
+        # kernel (sm__inst_executed_pipe_fp64 / (S_pad n_pad)), as DFMA-equivalent TFLOP/s against the FP64 peak
+        spad = (S + 1 + 127) // 128 * 128
+        npad32 = float(((batch.n + 31) // 32 * 32).sum())
+        fl = 2.0 * NCU_K1S_FP64_PER_PIXEL * spad * npad32
+        roofline_voigt = {"kernel": "voigt_slices_lane_kernel (K1s, sample-per-lane, emits int8 slice planes)",
+                          "bound": "fp64 vector pipe", "achieved": fl / t_voigt / 1e12, "peak": dgemm_tflops,
+                          "peak_pipe": FP64_PIPE_TFLOPS, "unit": "TFLOP/s (2 x FP64 instructions)",
+                          "frac": fl / t_voigt / 1e12 / dgemm_tflops, "frac_of_pipe": fl / t_voigt / 1e12 / FP64_PIPE_TFLOPS,
+                          "fp64_instructions_per_hypothesis_pixel": NCU_K1S_FP64_PER_PIXEL,
+                          "plane_write_gbs": 14.0 * spad * npad32 / t_voigt / 1e9, "hbm_peak_gbs": hbm_peak,
+                          "faddeeva_evals_per_s": 3.0 * S * float((batch.n_full + 6).sum()) / t_voigt,
+                          "ms_per_step": 1e3 * t_voigt,
+                          "peak_source": "cuBLAS DGEMM measured in this run; peak_pipe = DFMA/DMMA probe constant "
+                                         "(profiles/r01_probe_fp64.jsonl); instruction count from profiles/r02_ncu_slices_summary.txt"}
+    else:
+        wu_bytes = 16.0 * S * n_sum                                    # W and U written once (fp64)
+        roofline_voigt = {"kernel": "voigt_weights_lane_kernel (K1, sample-per-lane)", "bound": "fp64 vector pipe",
+                          "achieved": 2.0 * 58 * S * n_sum / t_voigt / 1e12, "peak": dgemm_tflops, "peak_pipe": FP64_PIPE_TFLOPS,
+                          "unit": "TFLOP/s (2 x FP64 instructions, 58 per hypothesis and pixel: profiles/r01_ncu_full_summary.txt)",
+                          "frac": 2.0 * 58 * S * n_sum / t_voigt / 1e12 / dgemm_tflops,
+                          "wu_write_gbs": wu_bytes / t_voigt / 1e9, "hbm_peak_gbs": hbm_peak,
+                          "faddeeva_evals_per_s": 3.0 * S * float((batch.n_full + 6).sum()) / t_voigt,
+                          "ms_per_step": 1e3 * t_voigt}
+    if slices:
+        dominant = "K1s voigt_slices_lane_kernel" if t_voigt > t_contract else "K2s contract_slices_tiles_kernel"
+    else:
+        dominant = "K1 voigt_weights_lane_kernel" if t_voigt > t_contract else "K2 " + k2_name.split(" ")[0]
 
     if rank == 0:
         cpu = None

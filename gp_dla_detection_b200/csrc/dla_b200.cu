@@ -135,9 +135,10 @@ struct dla_ctx {
   bool use_fused = false;            // DLA_B200_FUSED=1: fused_voigt_contract_kernel (W/U never leave the SM)
   bool use_slices = true;            // DLA_B200_CONTRACT=dmma turns the int8 tcgen05 contraction off (FP64 DMMA kernels)
   int k2s_mode = 0;                  // DLA_B200_K2S_MODE=1/2: diagnosis builds of the contraction (no MMA / no loads)
+  int k1q_variant = 0;               // DLA_B200_K1Q=0/1/2: Voigt kernel build when it runs alone (launch_chunk_slices)
   int k2s_stages = 5;                // DLA_B200_K2S_STAGES=3/5: ring depth of the contraction when it runs alone
   int overlap_chunks = 16;           // DLA_B200_OVERLAP_CHUNKS: chunks an overlapped batch is split into (at most)
-  bool overlap = true;               // DLA_B200_OVERLAP=0: contraction of chunk i NOT run under the Voigt kernel of chunk i + 1
+  bool overlap = false;               // DLA_B200_OVERLAP=0: contraction of chunk i NOT run under the Voigt kernel of chunk i + 1
   std::vector<SliceQuasar> h_sq;
   DevBuf d_sq, d_isc, d_csc;
   // slice-path workspace of one chunk: sample planes, table planes and scales, partial sums; two sets when chunks overlap
@@ -226,12 +227,12 @@ constexpr int NTEV = 7;
 template <typename... Args>
 static void launch_k2s(int mode, int stages, unsigned grid, cudaStream_t st, Args... args) {
   namespace sl = dla::sl;
-  if (mode == 1 && stages == 3) sl::contract_slices_tiles_kernel<1, 3><<<grid, sl::THREADS, sl::k2s_smem(3), st>>>(args...);
-  else if (mode == 2 && stages == 3) sl::contract_slices_tiles_kernel<2, 3><<<grid, sl::THREADS, sl::k2s_smem(3), st>>>(args...);
-  else if (mode == 1) sl::contract_slices_tiles_kernel<1, 5><<<grid, sl::THREADS, sl::k2s_smem(5), st>>>(args...);
-  else if (mode == 2) sl::contract_slices_tiles_kernel<2, 5><<<grid, sl::THREADS, sl::k2s_smem(5), st>>>(args...);
-  else if (stages == 3) sl::contract_slices_tiles_kernel<0, 3><<<grid, sl::THREADS, sl::k2s_smem(3), st>>>(args...);
-  else sl::contract_slices_tiles_kernel<0, 5><<<grid, sl::THREADS, sl::k2s_smem(5), st>>>(args...);
+  if (mode == 1 && stages == 3) sl::contract_slices_tiles_kernel<1, 3><<<grid, sl::K2S_THREADS, sl::k2s_smem(3), st>>>(args...);
+  else if (mode == 2 && stages == 3) sl::contract_slices_tiles_kernel<2, 3><<<grid, sl::K2S_THREADS, sl::k2s_smem(3), st>>>(args...);
+  else if (mode == 1) sl::contract_slices_tiles_kernel<1, 5><<<grid, sl::K2S_THREADS, sl::k2s_smem(5), st>>>(args...);
+  else if (mode == 2) sl::contract_slices_tiles_kernel<2, 5><<<grid, sl::K2S_THREADS, sl::k2s_smem(5), st>>>(args...);
+  else if (stages == 3) sl::contract_slices_tiles_kernel<0, 3><<<grid, sl::K2S_THREADS, sl::k2s_smem(3), st>>>(args...);
+  else sl::contract_slices_tiles_kernel<0, 5><<<grid, sl::K2S_THREADS, sl::k2s_smem(5), st>>>(args...);
 }
 
 // The exact-slice path of one chunk (slices_path.cuh): K0s tables and K1s Voigt -> int8 planes on the compute stream,
@@ -271,12 +272,17 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
   const int nseg = std::min(dla::K1S_NSEG_MAX, std::max(dla::K1S_NSEG_MIN, (nch + 19) / 20));
   {
     const int cmax = (nch + nseg - 1) / nseg;   // 16-pixel chunks per segment
-    const int lam_cap = 16 * cmax + 8;
-    const size_t smem = (size_t)lam_cap * 8 + (size_t)2 * sl::NSL * 3 * sl::K1Q_THREADS * 4;
+    const int lam_cap = 16 * cmax + 8, px_cap = 16 * cmax;
+    const int variant = ov ? 2 : c->k1q_variant;   // 0: 168 registers, records in shared memory; 1: 128 registers, same; 2: 128, records from L1
+    const size_t smem = (size_t)lam_cap * 8 + (variant == 2 ? 0 : (size_t)px_cap * 48) + (size_t)2 * sl::NSL * 3 * sl::K1Q_THREADS * 4;
     if (smem > 100 * 1024) BAD_ARG(c, "a quasar has too many pixels for the Voigt kernel's shared-memory staging");
-    sl::voigt_slices_lane_kernel<<<(unsigned)((int64_t)ch.nq * nsb * nseg), sl::K1Q_THREADS, smem, sa>>>(
-        in.desc, in.sq, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_isc.as<double2>(), c->d_etab256.as<double>(),
-        Aw, Au, aux, lam_cap, nseg);
+    const unsigned grid = (unsigned)((int64_t)ch.nq * nsb * nseg);
+#define K1Q_ARGS in.desc, in.sq, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_isc.as<double2>(), \
+                 c->d_etab256.as<double>(), Aw, Au, aux, lam_cap, px_cap, nseg
+    if (variant == 2) sl::voigt_slices_lane_kernel<4, false><<<grid, sl::K1Q_THREADS, smem, sa>>>(K1Q_ARGS);
+    else if (variant == 1) sl::voigt_slices_lane_kernel<4, true><<<grid, sl::K1Q_THREADS, smem, sa>>>(K1Q_ARGS);
+    else sl::voigt_slices_lane_kernel<3, true><<<grid, sl::K1Q_THREADS, smem, sa>>>(K1Q_ARGS);
+#undef K1Q_ARGS
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[2], sa));
   if (ov) {
@@ -644,13 +650,16 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     c->k2_rowsplit = k2 && strcmp(k2, "rowsplit") == 0;
     c->num_sms = prop.multiProcessorCount;
     const char* ct = getenv("DLA_B200_CONTRACT");
-    c->use_slices = !(ct && strcmp(ct, "dmma") == 0) && !c->use_fused && !c->force_tile_k2 && !c->k2_rowsplit;
+    c->use_slices = !(ct && strcmp(ct, "dmma") == 0) && !(k2 && strcmp(k2, "dmma") == 0) && !c->use_fused &&
+                    !c->force_tile_k2 && !c->k2_rowsplit;
     const char* km = getenv("DLA_B200_K2S_MODE");
     c->k2s_mode = km ? atoi(km) : 0;
+    const char* kq = getenv("DLA_B200_K1Q");
+    if (kq) c->k1q_variant = std::max(0, std::min(2, atoi(kq)));
     const char* ks = getenv("DLA_B200_K2S_STAGES");
     c->k2s_stages = (ks && atoi(ks) == 3) ? 3 : 5;
     const char* ov = getenv("DLA_B200_OVERLAP");
-    c->overlap = !(ov && strcmp(ov, "0") == 0);
+    c->overlap = ov && strcmp(ov, "1") == 0;   // measured: no gain (the two kernels contend for shared-memory bandwidth)
     const char* tp = getenv("DLA_B200_TRACE");
     if (tp && *tp) {
       c->trace_path = tp;
@@ -676,10 +685,12 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<0, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<1, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<2, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-  CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel<4, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::chol_rows_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::chol_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::K2C_SMEM));
-  CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::voigt_slices_lane_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
   CREATE_TRY(cudaFuncSetAttribute(dla::contract_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   dla::K2_STAGES * dla::STAGE_DOUBLES * 8 + 64));
   CREATE_TRY(cudaFuncSetAttribute(dla::fused_voigt_contract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -39,6 +39,7 @@ constexpr int UNITS = 5;                       // column units per sample block:
 constexpr int K2S_STAGE = A_STEP7 + B_STEP64;  // 43 008
 // ring depth of the contraction: 5 when it has the SM to itself, 3 (130 KB) when Voigt CTAs of the next chunk share it
 constexpr size_t k2s_smem(int stages) { return (size_t)stages * K2S_STAGE + 1024 + 256; }
+constexpr int K2S_THREADS = 320;               // warp 0 TMA producer, warp 1 MMA issue, warps 2..9 epilogue (two per TMEM lane quarter)
 constexpr int K1Q_THREADS = 128;               // one CTA = the 128 hypotheses of a sample block x one spectrum segment
 
 // CTA residency trace (diagnosis, DLA_B200_TRACE=<file>): {kernel id, SM id, start ns, end ns} per CTA
@@ -236,15 +237,16 @@ __device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NS
   out[0] = __byte_perm(t6, t7, 0x5410);
 }
 
-#ifndef DLA_K1Q_MINB
-#define DLA_K1Q_MINB 4   // resident CTAs per SM (4 x 128 threads -> 128 registers)
-#endif
-__global__ void __launch_bounds__(K1Q_THREADS, DLA_K1Q_MINB)
+// MINB: resident CTAs per SM the kernel is compiled for (3 -> 168 registers, 4 -> 128).  PXS: the per-pixel records
+// {omega2, noise, mu, flux, 1/c_w, 1/c_u} of the segment are staged in shared memory (px_cap pixels, 48 B each);
+// otherwise they are warp-uniform global loads (L1 hits) and a CTA needs 26 KB only.
+template <int MINB, bool PXS>
+__global__ void __launch_bounds__(K1Q_THREADS, MINB)
 voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar* __restrict__ sq, int q0, int nsb /* 128-sample blocks */,
                          int64_t S, const double* __restrict__ offset_sorted, const double* __restrict__ nhi_sorted,
                          const double* __restrict__ padded_wavelengths, const double2* __restrict__ pix4,
                          const double2* __restrict__ isc, const double* __restrict__ etab256, int8_t* __restrict__ Wplanes,
-                         int8_t* __restrict__ Uplanes, double* __restrict__ aux, int lam_cap, int nseg) {
+                         int8_t* __restrict__ Uplanes, double* __restrict__ aux, int lam_cap, int px_cap, int nseg) {
   extern __shared__ __align__(16) double k1q_smem[];
   __shared__ double etab_s[256];
   const bool tracing = g_trace != nullptr;
@@ -262,14 +264,20 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
   const int lbase = max(4 * g0 - 2, 0), llast = min(4 * g1 + 5, Pm1);
   const int j0 = min(4 * g0, n), j1 = min(4 * g1, n);                     // kept pixels this segment emits
   const int nsteps = (g1 > g0) ? g1 - g0 + 2 : 0;
-  // shared: the segment's wavelengths and the piece staging only; the per-pixel records are warp-uniform global loads
-  // (L1 hits), which keeps a CTA at 26 KB so that three of them fit on an SM beside the contraction of the previous chunk
   double* lam_s = k1q_smem;
-  uint32_t* stg_s = reinterpret_cast<uint32_t*>(k1q_smem + lam_cap) + tid;   // [14 pieces][3 steps][128 lanes]
+  double2* px_s = reinterpret_cast<double2*>(k1q_smem + lam_cap);
+  double2* sc_s = px_s + 2 * (PXS ? px_cap : 0);
+  uint32_t* stg_s = reinterpret_cast<uint32_t*>(sc_s + (PXS ? px_cap : 0)) + tid;   // [14 pieces][3 steps][128 lanes]
   for (int i = tid; i < 256; i += K1Q_THREADS) etab_s[i] = etab256[i];
   {
     const double* lam_g = padded_wavelengths + d.pad_off;
     for (int i = tid; i < 4 * nsteps; i += K1Q_THREADS) lam_s[i] = __ldg(lam_g + min(max(4 * g0 - 2 + i, lbase), llast));
+    if (PXS) {
+      const double2* px_g = pix4 + 2 * (d.pix_off + j0);
+      for (int i = tid; i < 2 * (j1 - j0); i += K1Q_THREADS) px_s[i] = __ldg(px_g + i);
+      const double2* sc_g = isc + d.pix_off + j0;
+      for (int i = tid; i < j1 - j0; i += K1Q_THREADS) sc_s[i] = __ldg(sc_g + i);
+    }
   }
   __syncthreads();
   const int64_t s = (int64_t)sb * K1Q_THREADS + tid;
@@ -286,8 +294,8 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
     nc1[j] = ncw[j] * g_lines.g1p[j];
     nc2[j] = ncw[j] * g_lines.gq[2];
   }
-  const double2* px = pix4 + 2 * d.pix_off;   // indexed by 2 * kept pixel
-  const double2* sc = isc + d.pix_off;        // indexed by kept pixel
+  const double2* px = PXS ? px_s - 2 * j0 : pix4 + 2 * d.pix_off;   // indexed by 2 * kept pixel
+  const double2* sc = PXS ? sc_s - j0 : isc + d.pix_off;            // indexed by kept pixel
   const int jdead = (j1 > j0) ? j0 : 0;  // a live pixel of this segment stands in for dead ones (values discarded)
   const int gfull = n >> 2;
   const int64_t S_pad = (int64_t)nsb * SB;
@@ -326,7 +334,7 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
         const int j = 4 * g + h;
-        const double2 is = have_px ? __ldg(sc + ((j < n) ? j : jdead)) : make_double2(0.0, 0.0);
+        const double2 is = have_px ? sc[(j < n) ? j : jdead] : make_double2(0.0, 0.0);
         mw[h] = fma(w[h], is.x, 1.0);
         mu_[h] = fma(u[h], is.y, 1.5);
       }
@@ -417,10 +425,9 @@ __device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, u
   }
 }
 
-// launch bounds: the second number only caps the registers at 80 (shared memory allows one CTA per SM anyway), so that
-// three Voigt CTAs of the next chunk (128 registers x 128 threads each) fit beside this kernel on an SM
+// launch bounds: the second number only caps the registers (shared memory allows one CTA per SM anyway)
 template <int MODE, int K2S_STAGES>
-__global__ void __launch_bounds__(THREADS, 4)
+__global__ void __launch_bounds__(K2S_THREADS, 2)
 contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq, int nsb, const int8_t* __restrict__ Aw,
                              const int8_t* __restrict__ Au, const int8_t* __restrict__ Bt, const double* __restrict__ colscale,
                              double* __restrict__ G) {
@@ -442,7 +449,7 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
       bar_init(&empty[s], 1);
     }
     bar_init(tfull, 1);
-    bar_init(tempty, 4);   // one arrive per epilogue warp
+    bar_init(tempty, 8);   // one arrive per epilogue warp
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -501,6 +508,7 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
     }
   } else {
     const int quarter = warp & 3;             // TMEM lanes [32 q, 32 q + 32) belong to the warps with warp % 4 == q
+    const int half = (warp - 2) >> 2;         // the two warps of a quarter split the columns
     const int row = quarter * 32 + lane;
     const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
     const int64_t S_pad = (int64_t)nsb * SB;
@@ -511,9 +519,9 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
       tc_fence_after();
       double* grow = G + ((int64_t)tl.ql * S_pad + (int64_t)tl.sb * SB + row) * GCOLS + tl.col0;
       const double* cs = colscale + (int64_t)tl.ql * GCOLS + tl.col0;
-      const int nc8 = tl.N / 8;
+      const int nc8h = tl.N / 16;
 #pragma unroll 1
-      for (int c8 = 0; c8 < nc8; ++c8) {
+      for (int c8 = half * nc8h; c8 < (half + 1) * nc8h; ++c8) {
         uint32_t r[NSL][8];
 #pragma unroll
         for (int dgn = 0; dgn < NSL; ++dgn) tmem_ld8(tlane + (uint32_t)(dgn * tl.N + c8 * 8), r[dgn]);

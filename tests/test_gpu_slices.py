@@ -1,0 +1,156 @@
+"""-m gpu: the exact-slice int8 tcgen05 contraction (csrc/slices_path.cuh), the default path for k <= 20, three lines
+and the as-written gather (log_mvnpdf_low_rank.m:22, :26-28 off the FP64 pipe).
+
+  * it IS the path that runs (dla_timing.contraction == 1) and it meets the north_star gates against the C oracle
+  * it agrees with the FP64 DMMA kernels (DLA_B200_CONTRACT=dmma) far inside those gates
+  * spectra shorter than a K step / a segment / a 16-pixel chunk (padding chunks, segments with no live pixel)
+  * a quasar with huge dynamic range of the noise variance (per-pixel power-of-two scales, column scales)
+  * NaN inputs poison exactly what they poison in fp64
+  * chunked and overlapped schedules give bit-identical results
+  * batches the slice path must not take (masked gather, num_lines != 3, k > 20) fall back to the DMMA kernels
+All through the C ABI.
+"""
+import copy
+
+import numpy as np
+import pytest
+
+from gp_dla_detection_b200.process_qsos import DlaContext, PackedBatch
+from tests.helpers import ATOL_LOG_POST, RTOL_SAMPLE_LL, assert_parity, oracle_batch, prepared_config
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(prepared, samples, k, S, lp_dla, lp_no, num_lines=3, workspace_bytes=0):
+    with DlaContext(k=k, num_lines=num_lines, num_samples=S, workspace_bytes=workspace_bytes) as ctx:
+        ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+        out = ctx.eval_batch(PackedBatch(prepared, k), lp_dla, lp_no)
+        out["_timing"] = ctx.timing()
+    return out
+
+
+def test_slice_path_runs_and_meets_the_gates(oracle, monkeypatch):
+    Q, S = 6, 1500   # 12 sample blocks of 128, the last one partial
+    params, model, samples, sp, prepared = prepared_config("config1", Q, S)
+    got = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 1, "the int8 slice contraction is not the path that ran"
+    assert got["_timing"]["ms_chol"] > 0
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    worst = assert_parity(got, ref)
+    monkeypatch.setenv("DLA_B200_CONTRACT", "dmma")
+    dmma = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert dmma["_timing"]["contraction"] == 0
+    a, b = got["sample_log_likelihoods_dla"], dmma["sample_log_likelihoods_dla"]
+    both = float(np.max(np.abs(a - b)))
+    print(f"slices vs oracle worst rel {worst:.2e}; slices vs DMMA worst abs {both:.2e}")
+    assert both <= 2e-9     # the two contractions differ by rounding only (values are O(1e2..1e3))
+    assert np.array_equal(got["map_ind"], dmma["map_ind"])
+
+
+@pytest.mark.parametrize("n_keep", [1, 7, 15, 16, 17, 33, 64, 65, 129])
+def test_short_spectra(oracle, n_keep):
+    """Spectra of 1..129 kept pixels: fewer 16-pixel chunks than segments, chunks wholly beyond n, one K step."""
+    S = 300
+    params, model, samples, sp, prepared = prepared_config("config1", 2, S)
+    short = []
+    for p in prepared:
+        p = copy.deepcopy(p)
+        # keep the first n_keep pixels: every per-kept-pixel array and the padded grid shrink together
+        p.flux, p.noise_variance, p.mu, p.omega2 = (x[:n_keep].copy() for x in (p.flux, p.noise_variance, p.mu, p.omega2))
+        p.M = np.asfortranarray(np.asarray(p.M)[:n_keep])
+        p.profile_index = p.profile_index[:n_keep].copy()
+        p.padded_wavelengths = p.padded_wavelengths[:n_keep + 6].copy()
+        p.n, p.n_full = n_keep, n_keep
+        short.append(p)
+    got = _run(short, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 1
+    ref = oracle_batch(oracle, short, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(got, ref)
+
+
+def test_wide_dynamic_range_of_the_noise(oracle):
+    """Noise variance from 1e-7 to 1e+3 inside ONE spectrum, |flux| up to 30: the per-pixel scales c_w, c_u span
+    33 binary orders and the column scales follow the few low-noise pixels."""
+    S = 400
+    params, model, samples, sp, prepared = prepared_config("config1", 3, S)
+    rng = np.random.default_rng(7)
+    hard = []
+    for p in prepared:
+        p = copy.deepcopy(p)
+        p.noise_variance = 10.0 ** rng.uniform(-7, 3, p.n)
+        p.flux = p.flux * np.where(rng.random(p.n) < 0.02, 30.0, 1.0)
+        hard.append(p)
+    got = _run(hard, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 1
+    ref = oracle_batch(oracle, hard, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    worst = assert_parity(got, ref)
+    print(f"noise variance 1e-7..1e3: worst per-sample rel err {worst:.2e}")
+
+
+def test_nonfinite_inputs_poison_like_fp64(oracle):
+    """A NaN flux pixel or a NaN entry of M makes every likelihood of THAT quasar NaN, and only of that quasar
+    (the slices of a NaN are garbage integers: the NaN travels through r'D^-1 r and the column scales instead)."""
+    S = 256
+    params, model, samples, sp, prepared = prepared_config("config1", 4, S)
+    bad = [copy.deepcopy(p) for p in prepared]
+    bad[0].flux[100] = np.nan
+    M1 = np.array(bad[1].M)
+    M1[200, 3] = np.nan
+    bad[1].M = np.asfortranarray(M1)
+    bad[2].noise_variance[50] = np.nan
+    got = _run(bad, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 1
+    ref = oracle_batch(oracle, bad, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    ll = got["sample_log_likelihoods_dla"]
+    assert np.all(np.isnan(ll[:3]))
+    assert np.all(np.isnan(got["log_likelihoods_no_dla"][:3]))
+    assert np.all(np.isnan(ref["sample_log_likelihoods_dla"][:3]))
+    rel = np.abs(ll[3] - ref["sample_log_likelihoods_dla"][3]) / np.abs(ref["sample_log_likelihoods_dla"][3])
+    assert rel.max() <= RTOL_SAMPLE_LL
+
+
+def test_schedules_are_bitwise_identical(monkeypatch):
+    """One chunk, many chunks (small workspace) and the overlapped two-stream schedule (DLA_B200_OVERLAP=1: contraction
+    of chunk i under the Voigt kernel of chunk i + 1, alternating plane sets) must agree bit for bit."""
+    Q, S = 14, 700
+    params, model, samples, sp, prepared = prepared_config("config3", Q, S)   # ragged lengths
+    one = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert one["_timing"]["contraction"] == 1
+    many = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla, workspace_bytes=64 << 20)
+    assert many["_timing"]["chunks"] > one["_timing"]["chunks"]
+    monkeypatch.setenv("DLA_B200_OVERLAP", "1")
+    ovl = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert ovl["_timing"]["chunks"] >= 2
+    monkeypatch.setenv("DLA_B200_K2S_STAGES", "3")
+    monkeypatch.setenv("DLA_B200_OVERLAP", "0")
+    st3 = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    for other in (many, ovl, st3):
+        for key in ("sample_log_likelihoods_dla", "log_likelihoods_no_dla", "log_posteriors_dla", "map_ind"):
+            assert np.array_equal(one[key], other[key], equal_nan=True), key
+
+
+@pytest.mark.parametrize("variant", ["1", "2"])
+def test_voigt_kernel_builds(oracle, monkeypatch, variant):
+    """DLA_B200_K1Q: the 128-register builds of the slice-emitting Voigt kernel (records in shared memory / from L1)."""
+    monkeypatch.setenv("DLA_B200_K1Q", variant)
+    params, model, samples, sp, prepared = prepared_config("config3", 4, 300)
+    got = _run(prepared, samples, 20, 300, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 1
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(got, ref)
+
+
+def test_fallbacks_to_the_dmma_kernels(oracle):
+    """Masked gather, num_lines != 3 and k > 20 are not slice-path batches: the FP64 kernels run them."""
+    S = 200
+    params, model, samples, sp, prepared = prepared_config("config3", 3, S, "intended")
+    got = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 0
+    params, model, samples, sp, prepared = prepared_config("config1", 2, S)
+    got = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla, num_lines=5)
+    assert got["_timing"]["contraction"] == 0
+    params, model, samples, sp, prepared = prepared_config("config5", 2, S)
+    got = _run(prepared, samples, 40, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 0
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(got, ref)
