@@ -21,7 +21,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
     "--shared", "-Xcompiler", "-fPIC",
-    "-cudart", "static",
+    "-cudart", "static", "-ldl",
     "-Xptxas", "-v",
 ]
 

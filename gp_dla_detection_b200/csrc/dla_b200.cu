@@ -9,9 +9,13 @@
 #include <string.h>
 
 #include <algorithm>
+#include <exception>
+#include <new>
 #include <string>
 #include <thread>
 #include <vector>
+
+#include <nvtx3/nvToolsExt.h>   // header-only: ranges are no-ops unless a profiler injects its library
 
 #include "kernels.cuh"
 #include "slices_path.cuh"
@@ -22,6 +26,18 @@ using dla::sl::SliceQuasar;
 namespace {
 
 thread_local std::string g_create_error;
+
+// NVTX range over a scope: the host side of one stage (copies, K0..K3 launches) of one chunk, as a timeline tool sees it
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+
+// DLA_B200_VERBOSE=1: one line per chunk on stderr, like fprintf_debug in process_qsos.m:93-94, :219
+bool g_verbose = [] {
+  const char* v = getenv("DLA_B200_VERBOSE");
+  return v && *v && strcmp(v, "0") != 0;
+}();
 
 struct DevBuf {
   void* p = nullptr;
@@ -258,6 +274,7 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
   if (ov && set.busy) CU_TRY(c, cudaStreamWaitEvent(sa, set.done, 0));   // the chunk that last used this set has finished
   if (time_it) CU_TRY(c, cudaEventRecord(tev[0], sa));
   {
+    NvtxRange r("dla K0s tables");
     dim3 grid((unsigned)((ch.max_npad + 255) / 256), (unsigned)ch.nq);
     dla::pack_pixels_kernel<<<grid, 256, 0, sa>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
     sl::pixel_scales_kernel<<<grid, 256, 0, sa>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, c->d_isc.as<double2>(),
@@ -271,6 +288,7 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
   const int nch = 2 * ch.max_nks;
   const int nseg = std::min(dla::K1S_NSEG_MAX, std::max(dla::K1S_NSEG_MIN, (nch + 19) / 20));
   {
+    NvtxRange r("dla K1s voigt -> int8 planes");
     const int cmax = (nch + nseg - 1) / nseg;   // 16-pixel chunks per segment
     const int lam_cap = 16 * cmax + 8, px_cap = 16 * cmax;
     const int variant = ov ? 2 : c->k1q_variant;   // 0: 168 registers, records in shared memory; 1: 128 registers, same; 2: 128, records from L1
@@ -291,6 +309,7 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[3], sb));
   {
+    NvtxRange r("dla K2s tcgen05 contraction");
     const int64_t ntiles = (int64_t)ch.nq * nsb * sl::UNITS;
     const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
     launch_k2s(c->k2s_mode, ov ? 3 : c->k2s_stages, grid, sb, in.sq, ch.q0, ch.nq, nsb, (const int8_t*)Aw, (const int8_t*)Au,
@@ -298,6 +317,7 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[4], sb));
   {
+    NvtxRange r("dla K2c cholesky + K3 reduce");
     dim3 grid((unsigned)(nsb * (sl::SB / sl::K2C_ROWS)), (unsigned)ch.nq);
     sl::chol_rows_kernel<<<grid, sl::K2C_ROWS * 4, sl::K2C_SMEM, sb>>>(in.desc, ch.q0, nsb, S, G, aux, d_perm, sample_ll_chunk,
                                                                       ll_no, k, nseg);
@@ -748,7 +768,7 @@ void dla_destroy(dla_ctx* c) {
   delete c;
 }
 
-int dla_set_samples(dla_ctx* c, const double* offset_samples, const double* nhi_samples) {
+static int dla_set_samples_impl(dla_ctx* c, const double* offset_samples, const double* nhi_samples) {
   if (!c) return DLA_ERR_BAD_ARG;
   if (!offset_samples || !nhi_samples) BAD_ARG(c, "dla_set_samples: NULL pointer");
   CU_TRY(c, cudaSetDevice(c->device));
@@ -857,7 +877,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
     const long double target = total / nch;
     // quasar-count cap of a chunk: the persistent contraction runs nq * nsb tiles in waves of num_sms; among the
     // counts within 1/8 below what the budget allows, take the one whose last wave is fullest (up to 1 % of K2)
-    int64_t nq_cap = INT32_MAX;
+    int64_t nq_cap = 65535;   // the per-quasar kernels take the quasar index as gridDim.y
     if (Q > 0) {
       long double max_bts = 0;
       for (int64_t q = 0; q < Q; ++q) max_bts = std::max(max_bts, quasar_bytes(c->h_desc[(size_t)q], gq));
@@ -958,6 +978,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
 // H2D of the inputs of chunk i on stream st (chunk 0 also carries the descriptors of the whole
 // batch); records the chunk's "inputs resident" event.
 static int upload_chunk(dla_ctx* c, size_t i, cudaStream_t st) {
+  NvtxRange r("dla H2D chunk inputs");
   const Chunk& ch = c->chunks[i];
   const auto& h = c->hin;
   const int k = c->p.k;
@@ -990,7 +1011,11 @@ static int upload_chunk(dla_ctx* c, size_t i, cudaStream_t st) {
 
 // kernels of chunk i on the compute stream, after its inputs are resident
 static int run_chunk(dla_ctx* c, size_t i) {
+  NvtxRange r("dla chunk kernels");
   const Chunk& ch = c->chunks[i];
+  if (g_verbose)
+    fprintf(stderr, "dla_b200: chunk %zu of %zu: quasars %d..%d of %lld, %s contraction\n", i + 1, c->chunks.size(), ch.q0 + 1,
+            ch.q0 + ch.nq, (long long)c->Q, ch.slices ? "int8 slice" : "FP64 DMMA");
   const int64_t S = c->p.num_samples;
   Inputs in{c->d_desc.as<QuasarDesc>(), c->d_padded.as<double>(), c->d_flux.as<double>(), c->d_mu.as<double>(),
             c->d_om.as<double>(), c->d_nv.as<double>(), c->d_M.as<double>(), c->d_pidx.as<int32_t>(),
@@ -1017,7 +1042,7 @@ static int run_chunk(dla_ctx* c, size_t i) {
   return DLA_OK;
 }
 
-int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
+static int dla_stage_batch_impl(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
                     const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
                     const double* mu, const double* omega2, const double* noise_variance, const double* M,
                     const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
@@ -1041,7 +1066,7 @@ int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t
   return DLA_OK;
 }
 
-int dla_run_staged(dla_ctx* c) {
+static int dla_run_staged_impl(dla_ctx* c) {
   if (!c) return DLA_ERR_BAD_ARG;
   if (!c->staged) {
     c->err = "dla_run_staged: no batch staged";
@@ -1095,7 +1120,7 @@ static int download_small(dla_ctx* c, cudaStream_t st, double* ll_no_dla, double
   return DLA_OK;
 }
 
-int dla_fetch_staged(dla_ctx* c, double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
+static int dla_fetch_staged_impl(dla_ctx* c, double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
                      double* log_post_dla, double* model_posteriors, int32_t* map_index) {
   if (!c) return DLA_ERR_BAD_ARG;
   if (!c->ran) {
@@ -1159,7 +1184,7 @@ static int run_pipelined(dla_ctx* c, double* sample_ll, double* ll_no_dla, doubl
   return DLA_OK;
 }
 
-int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
+static int dla_eval_batch_impl(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr,
                    const double* padded_wavelengths, const int32_t* profile_index, const double* flux,
                    const double* mu, const double* omega2, const double* noise_variance, const double* M,
                    const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla,
@@ -1174,7 +1199,7 @@ int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t*
   return run_pipelined(c, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index);
 }
 
-int dla_set_model(dla_ctx* c, int64_t n_rest, const double* rest_wavelengths, const double* mu, const double* M,
+static int dla_set_model_impl(dla_ctx* c, int64_t n_rest, const double* rest_wavelengths, const double* mu, const double* M,
                   const double* log_omega, const dla_prep_params* prep) {
   if (!c) return DLA_ERR_BAD_ARG;
   if (!rest_wavelengths || !mu || !M || !log_omega || !prep) BAD_ARG(c, "dla_set_model: NULL pointer");
@@ -1266,7 +1291,7 @@ static void select_spectra(const dla_prep_params pp, dla_ctx::SpectraStage* stp,
   st.nkept = nkept;
 }
 
-int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const double* wavelengths, const double* flux,
+static int dla_eval_spectra_impl(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const double* wavelengths, const double* flux,
                      const double* noise_variance, const uint8_t* pixel_mask, const double* z_qso,
                      const double* log_prior_dla, const double* log_prior_no_dla, int32_t mask_gather,
                      double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla,
@@ -1362,7 +1387,7 @@ int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const doubl
   return DLA_OK;
 }
 
-int dla_train_set_data(dla_ctx* c, int64_t Q, int64_t n, const double* y, const double* l1pz, const double* nv) {
+static int dla_train_set_data_impl(dla_ctx* c, int64_t Q, int64_t n, const double* y, const double* l1pz, const double* nv) {
   if (!c) return DLA_ERR_BAD_ARG;
   if (!y || !l1pz || !nv) BAD_ARG(c, "dla_train_set_data: NULL pointer");
   if (Q < 1 || n < 1 || n > (1 << 20) || Q > (1 << 26)) BAD_ARG(c, "dla_train_set_data: sizes out of range");
@@ -1383,7 +1408,7 @@ int dla_train_set_data(dla_ctx* c, int64_t Q, int64_t n, const double* y, const 
   return DLA_OK;
 }
 
-int dla_train_objective(dla_ctx* c, const double* x, int32_t apply_priors, double* f, double* g) {
+static int dla_train_objective_impl(dla_ctx* c, const double* x, int32_t apply_priors, double* f, double* g) {
   if (!c) return DLA_ERR_BAD_ARG;
   if (!x || !f || !g) BAD_ARG(c, "dla_train_objective: NULL pointer");
   if (c->tQ == 0) {
@@ -1486,7 +1511,7 @@ int dla_get_timing(const dla_ctx* c, dla_timing* out) {
   return DLA_OK;
 }
 
-int dla_voigt(dla_ctx* c, const double* lambdas, int64_t num_points, double z, double N, int32_t num_lines,
+static int dla_voigt_impl(dla_ctx* c, const double* lambdas, int64_t num_points, double z, double N, int32_t num_lines,
               double* profile) {
   if (!c) return DLA_ERR_BAD_ARG;
   if (!lambdas || !profile) BAD_ARG(c, "dla_voigt: NULL pointer");
@@ -1519,7 +1544,7 @@ int dla_voigt(dla_ctx* c, const double* lambdas, int64_t num_points, double z, d
   return rc;
 }
 
-int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const double* M, const double* d,
+static int dla_log_mvnpdf_low_rank_impl(dla_ctx* c, const double* y, const double* mu, const double* M, const double* d,
                             int64_t n, int32_t k, double* log_p) {
   if (!c) return DLA_ERR_BAD_ARG;
   if (!y || !mu || !M || !d || !log_p) BAD_ARG(c, "dla_log_mvnpdf_low_rank: NULL pointer");
@@ -1580,6 +1605,90 @@ int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const
 #undef SEAM_TRY
   cleanup();
   return DLA_OK;
+}
+
+
+}  // extern "C" (implementations)
+
+// No C++ exception crosses the ABI (std::bad_alloc of the host-side vectors, std::system_error of the helper thread):
+// every entry point that can throw runs inside this guard.  After any failure the streams are drained, so that no
+// copy still reads or writes caller memory when the call returns (the header's promise).
+static void drain_after_failure(dla_ctx* c, bool reset_state) {
+  if (!c) return;
+  for (cudaStream_t st : {c->s_in, c->stream, c->stream2, c->s_out})
+    if (st) cudaStreamSynchronize(st);
+  cudaGetLastError();
+  for (auto& set : c->sset) set.busy = false;
+  c->slice_chunks = 0;
+  c->hin = {};
+  if (reset_state) {   // a CUDA / allocation failure: whatever was staged or computed is not to be trusted
+    c->staged = false;
+    c->ran = false;
+  }
+}
+template <typename F>
+static int guarded(dla_ctx* c, F&& f) {
+  int rc;
+  try {
+    rc = f();
+  } catch (const std::bad_alloc&) {
+    if (c) c->err = "host allocation failed (std::bad_alloc)";
+    rc = DLA_ERR_OOM;
+  } catch (const std::exception& e) {
+    if (c) c->err = std::string("unexpected C++ exception: ") + e.what();
+    rc = DLA_ERR_CUDA;
+  } catch (...) {
+    if (c) c->err = "unexpected C++ exception";
+    rc = DLA_ERR_CUDA;
+  }
+  if (rc != DLA_OK) drain_after_failure(c, rc != DLA_ERR_BAD_ARG && rc != DLA_ERR_STATE);
+  return rc;
+}
+
+extern "C" {
+
+int dla_set_samples(dla_ctx* c, const double* offset_samples, const double* nhi_samples) {
+  return guarded(c, [&] { return dla_set_samples_impl(c, offset_samples, nhi_samples); });
+}
+
+int dla_stage_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr, const double* padded_wavelengths, const int32_t* profile_index, const double* flux, const double* mu, const double* omega2, const double* noise_variance, const double* M, const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla, const double* log_prior_no_dla) {
+  return guarded(c, [&] { return dla_stage_batch_impl(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M, min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla); });
+}
+
+int dla_run_staged(dla_ctx* c) {
+  return guarded(c, [&] { return dla_run_staged_impl(c); });
+}
+
+int dla_fetch_staged(dla_ctx* c, double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla, double* log_post_dla, double* model_posteriors, int32_t* map_index) {
+  return guarded(c, [&] { return dla_fetch_staged_impl(c, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index); });
+}
+
+int dla_eval_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64_t* pad_ptr, const double* padded_wavelengths, const int32_t* profile_index, const double* flux, const double* mu, const double* omega2, const double* noise_variance, const double* M, const double* min_z_dla, const double* max_z_dla, const double* log_prior_dla, const double* log_prior_no_dla, double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla, double* log_post_dla, double* model_posteriors, int32_t* map_index) {
+  return guarded(c, [&] { return dla_eval_batch_impl(c, Q, pix_ptr, pad_ptr, padded_wavelengths, profile_index, flux, mu, omega2, noise_variance, M, min_z_dla, max_z_dla, log_prior_dla, log_prior_no_dla, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index); });
+}
+
+int dla_set_model(dla_ctx* c, int64_t n_rest, const double* rest_wavelengths, const double* mu, const double* M, const double* log_omega, const dla_prep_params* prep) {
+  return guarded(c, [&] { return dla_set_model_impl(c, n_rest, rest_wavelengths, mu, M, log_omega, prep); });
+}
+
+int dla_eval_spectra(dla_ctx* c, int64_t Q, const int64_t* spec_ptr, const double* wavelengths, const double* flux, const double* noise_variance, const uint8_t* pixel_mask, const double* z_qso, const double* log_prior_dla, const double* log_prior_no_dla, int32_t mask_gather, double* sample_ll, double* ll_no_dla, double* ll_dla, double* log_post_no_dla, double* log_post_dla, double* model_posteriors, int32_t* map_index, double* min_z_out, double* max_z_out) {
+  return guarded(c, [&] { return dla_eval_spectra_impl(c, Q, spec_ptr, wavelengths, flux, noise_variance, pixel_mask, z_qso, log_prior_dla, log_prior_no_dla, mask_gather, sample_ll, ll_no_dla, ll_dla, log_post_no_dla, log_post_dla, model_posteriors, map_index, min_z_out, max_z_out); });
+}
+
+int dla_train_set_data(dla_ctx* c, int64_t Q, int64_t n, const double* y, const double* l1pz, const double* nv) {
+  return guarded(c, [&] { return dla_train_set_data_impl(c, Q, n, y, l1pz, nv); });
+}
+
+int dla_train_objective(dla_ctx* c, const double* x, int32_t apply_priors, double* f, double* g) {
+  return guarded(c, [&] { return dla_train_objective_impl(c, x, apply_priors, f, g); });
+}
+
+int dla_voigt(dla_ctx* c, const double* lambdas, int64_t num_points, double z, double N, int32_t num_lines, double* profile) {
+  return guarded(c, [&] { return dla_voigt_impl(c, lambdas, num_points, z, N, num_lines, profile); });
+}
+
+int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const double* M, const double* d, int64_t n, int32_t k, double* log_p) {
+  return guarded(c, [&] { return dla_log_mvnpdf_low_rank_impl(c, y, mu, M, d, n, k, log_p); });
 }
 
 }  // extern "C"

@@ -156,13 +156,14 @@ def initial_x(centered_rest_fluxes, k: int, params: Parameters = DEFAULT):
 
 
 def learn_qso_model(rest_wavelengths, mu, centered_rest_fluxes, lya_1pzs, rest_noise_variances, k: int = 20,
-                    params: Parameters = DEFAULT, device: int = 0, dist=None, max_iter: int = 4000, x0=None):
+                    params: Parameters = DEFAULT, device: int = 0, dist=None, max_iter: int = 2000, max_fun: int = 4000,
+                    x0=None):
     """learn_qso_model.m:77-111 with scipy's L-BFGS-B in place of minFunc.  Returns (LearnedModel, f, info)."""
     from scipy.optimize import minimize
     obj = TrainingObjective(centered_rest_fluxes, lya_1pzs, rest_noise_variances, k, device, dist)
     try:
         x0 = initial_x(centered_rest_fluxes, k, params) if x0 is None else np.asarray(x0, dtype=np.float64)
-        res = minimize(lambda x: obj(x), x0, jac=True, method="L-BFGS-B", options={"maxiter": max_iter, "maxcor": 100})
+        res = minimize(lambda x: obj(x), x0, jac=True, method="L-BFGS-B", options={"maxiter": max_iter, "maxfun": max_fun, "maxcor": 100})
     finally:
         obj.close()
     n = np.asarray(rest_wavelengths).shape[0]

@@ -10,6 +10,8 @@ library or a CUDA device is missing the calls raise.
 from __future__ import annotations
 
 import ctypes as C
+import logging
+import time
 from dataclasses import dataclass
 from typing import Sequence
 
@@ -17,6 +19,9 @@ import numpy as np
 
 from . import _lib
 from .set_parameters import DEFAULT, Parameters
+
+
+log = logging.getLogger("gp_dla_detection_b200")
 
 
 @dataclass
@@ -404,6 +409,19 @@ def process_qsos(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, 
     """
     k = model.M.shape[1]
     S = samples.offset_samples.shape[0]
+    t_start = time.perf_counter()
+    log.info("processing %d quasars x %d DLA hypotheses (k = %d) on cuda:%d ...", len(z_qsos), S, k, device)
+
+    def report(out):
+        # process_qsos.m:93-94, :207-219 (fprintf / fprintf_debug), once per batch and per quasar at DEBUG level
+        dt = time.perf_counter() - t_start
+        log.info(" took %0.3fs (%.1f quasars/s).", dt, len(z_qsos) / max(dt, 1e-9))
+        if log.isEnabledFor(logging.DEBUG):
+            for i, z in enumerate(z_qsos):
+                log.debug("quasar %i/%i (z_QSO = %0.4f): log p(D | z_QSO, no DLA) %0.2f, log p(D | z_QSO, DLA) %0.2f, "
+                          "log p(DLA | D, z_QSO) %0.2f", i + 1, len(z_qsos), z, out["log_likelihoods_no_dla"][i],
+                          out["log_likelihoods_dla"][i], out["log_posteriors_dla"][i])
+        return out
     if device_prep:
         # process_qsos.m:102-180 inside the library (dla_set_model + dla_eval_spectra)
         spectra = PackedSpectra(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, z_qsos)
@@ -421,7 +439,7 @@ def process_qsos(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, 
 
         class _Z:  # what finish_outputs reads from a PackedBatch
             Q, min_z_dla, max_z_dla = spectra.Q, out["min_z_dlas"], out["max_z_dlas"]
-        return finish_outputs(out, _Z, samples, log_priors_dla, log_priors_no_dla)
+        return report(finish_outputs(out, _Z, samples, log_priors_dla, log_priors_no_dla))
     prepared = [prepare_quasar(w, f, v, m, z, model, params, mask_gather)
                 for w, f, v, m, z in zip(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, z_qsos)]
     batch = PackedBatch(prepared, k)
@@ -435,4 +453,4 @@ def process_qsos(all_wavelengths, all_flux, all_noise_variance, all_pixel_mask, 
     finally:
         if own:
             ctx.close()
-    return finish_outputs(out, batch, samples, log_priors_dla, log_priors_no_dla)
+    return report(finish_outputs(out, batch, samples, log_priors_dla, log_priors_no_dla))
