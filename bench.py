@@ -349,6 +349,36 @@ def run_ours(args):
                        "interpolation and omega^2 scaling on the device (learned model resident)"}
     assert np.allclose(out2["log_likelihoods_dla"], out["log_likelihoods_dla"], rtol=1e-9)
 
+    # ---- one quasar per call: the reference's own loop shape (process_qsos.m:88 `for quasar_ind = 1:num_quasars`)
+    # with the per-spectrum MEX gateway: dla_set_samples + dla_set_model (both return at once when the arrays are
+    # the ones already resident) + dla_eval_spectra(Q = 1), host arrays in, host results out, every call.
+    nq1 = min(Q, 48)
+    singles = [PackedSpectra(sp.all_wavelengths[q:q + 1], sp.all_flux[q:q + 1], sp.all_noise_variance[q:q + 1],
+                             sp.all_pixel_mask[q:q + 1], sp.z_qsos[q:q + 1]) for q in range(nq1)]
+    out1 = ctx._alloc_outputs(1, alloc=pinned_alloc)
+
+    def one_by_one():
+        acc = 0.0
+        for q in range(nq1):
+            ctx.set_samples(samples.offset_samples, samples.nhi_samples)
+            ctx.set_model(make_workload.model, params)
+            o = ctx.eval_spectra(singles[q], sp.log_priors_dla[q:q + 1], sp.log_priors_no_dla[q:q + 1], "reference", out1)
+            acc += float(o["log_likelihoods_dla"][0])
+        return acc
+    one_by_one()
+    barrier()
+    t0 = time.perf_counter()
+    acc1 = one_by_one()
+    barrier()
+    q1_s = max_over_ranks(time.perf_counter() - t0)
+    tm1 = ctx.timing()
+    e2e_q1 = {"value": nq1 * world / q1_s, "unit": METRIC, "quasars_timed": nq1, "ms_per_call": 1e3 * q1_s / nq1,
+              "device_ms_per_call": tm1["ms_total"], "h2d_bytes_per_call": int(tm1["h2d_bytes"]),
+              "d2h_bytes_per_call": int(tm1["d2h_bytes"]),
+              "what": "Q = 1 per call, the shape of process_qsos.m's own loop: dla_set_samples + dla_set_model (unchanged "
+                      "arrays: two memcmp's) + dla_eval_spectra of ONE quasar, wall clock per call"}
+    assert np.isfinite(acc1) and abs(acc1 - float(out2["log_likelihoods_dla"][:nq1].sum())) <= 1e-6 * abs(acc1)
+
     # ---- rooflines ------------------------------------------------------------------------------
     peaks = {}
     try:
@@ -443,7 +473,7 @@ def run_ours(args):
         line = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": config_dict(args, world), "e2e": e2e, "e2e_from_spectra": e2e_raw,
+                "config": config_dict(args, world), "e2e": e2e, "e2e_from_spectra": e2e_raw, "e2e_q1": e2e_q1,
                 "gpu_launches": int(launches),
                 "clocks": clocks, "roofline": roofline, "roofline_voigt": roofline_voigt,
                 "dominant_kernel": dominant, "cpu_baseline": cpu,

@@ -15,9 +15,12 @@
 typedef size_t mwSize;
 typedef enum { mxREAL = 0, mxCOMPLEX = 1 } mxComplexity;
 
+typedef unsigned char mxLogical;
 typedef struct mxArray_shim {
   double *pr;
   mwSize m, n;
+  struct mxArray_shim **cells;   /* cell arrays (dla_process_mex.c): m * n elements */
+  mxLogical *logicals;           /* logical arrays */
 } mxArray;
 
 static inline double *mxGetPr(const mxArray *a) { return a->pr; }
@@ -25,7 +28,7 @@ static inline double mxGetScalar(const mxArray *a) { return a->pr[0]; }
 static inline mwSize mxGetNumberOfElements(const mxArray *a) { return a->m * a->n; }
 static inline mxArray *mxCreateDoubleMatrix(mwSize m, mwSize n, mxComplexity c) {
   (void)c;
-  mxArray *a = (mxArray *)malloc(sizeof(mxArray));
+  mxArray *a = (mxArray *)calloc(1, sizeof(mxArray));
   a->m = m; a->n = n;
   a->pr = (double *)calloc((m * n) > 0 ? (m * n) : 1, sizeof(double));
   return a;
@@ -42,7 +45,10 @@ static inline mxArray *mxCreateDoubleScalar(double v) {
   a->pr[0] = v;
   return a;
 }
-static inline int mxIsDouble(const mxArray *a) { (void)a; return 1; }
+static inline int mxIsDouble(const mxArray *a) { return a->pr != 0; }
+static inline const mxArray *mxGetCell(const mxArray *a, mwSize i) { return a->cells ? a->cells[i] : 0; }
+static inline int mxIsLogical(const mxArray *a) { return a->logicals != 0; }
+static inline mxLogical *mxGetLogicals(const mxArray *a) { return a->logicals; }
 static inline int mxIsComplex(const mxArray *a) { (void)a; return 0; }
 void mexErrMsgIdAndTxt(const char *id, const char *fmt, ...);
 int mexAtExit(void (*fn)(void));

@@ -161,7 +161,7 @@ def test_mex_shims_compile_and_link_against_the_c_abi(tmp_path):
     env = dict(os.environ); env.pop("CC", None)
     pkg = os.path.join(ROOT, "gp_dla_detection_b200")
     _lib.load()
-    for src in ("voigt.c", "dla_eval_mex.c"):
+    for src in ("voigt.c", "dla_eval_mex.c", "dla_process_mex.c"):
         out = tmp_path / (src + ".so")
         subprocess.run(["gcc", "-Wall", "-Werror", "-shared", "-fPIC", os.path.join(pkg, "mex", src), str(stub),
                         "-I", os.path.join(ROOT, "oracle", "shim"), "-I", os.path.join(ROOT, "include"),
