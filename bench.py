@@ -34,8 +34,9 @@ N_PIX, K_RANK = 1217, 20
 NCU_K2_DRAM_GB_PER_QUASAR = (3.257835 + 0.006098) / 16
 # the same for the int8 slice contraction (profiles/r02_ncu_slices_summary.txt: 2.919 GB read + 0.325 GB written by one
 # 16-quasar launch) and the FP64 instructions of the slice-emitting Voigt kernel per (hypothesis, pixel)
-NCU_K2S_DRAM_GB_PER_QUASAR = (2.919130 + 0.325005) / 16
-NCU_K1S_FP64_PER_PIXEL = 60.0
+NCU_K2S_DRAM_GB_PER_QUASAR = (2.894050 + 0.321743) / 16   # profiles/r02_ncu_slices_summary.txt
+NCU_K1S_FP64_PER_PIXEL = 56.84   # FP64-pipe warp instructions x 32 / (hypothesis, pixel) pairs, same file
+INT8_NOMINAL_TOPS = 4500.0       # dense 8-bit tensor peak NVIDIA quotes for B200 (= fp8)
 FP64_PIPE_TFLOPS = 37.1   # register-resident DMMA / DFMA loops, tools/probe_fp64.cu, profiles/r01_probe_fp64.jsonl
 # BASELINE.json configs as (rank, grid spacing, ragged masking, hypotheses); SURVEY.md 8(d)
 WORKLOADS = {
@@ -421,6 +422,10 @@ def run_ours(args):
         roofline = {"kernel": "contract_slices_tiles_kernel (K2s: exact-slice int8 tcgen05 contraction, 7 x 7 slices, "
                               "int32 TMEM accumulators, fp64 recombination)",
                     "bound": "tensor", "achieved": ach8, "peak": int8_peak, "unit": "TOP/s (int8)", "frac": ach8 / int8_peak,
+                    "peak_nominal": INT8_NOMINAL_TOPS, "frac_of_nominal": ach8 / INT8_NOMINAL_TOPS,
+                    "shape_bound": "the 7 x 7 slice scheme issues MMAs of 32..256 columns; measured cost max(N/2, 64 + N/6) clocks each "
+                                   "(profiles/r02_probe_umma.jsonl) caps a 64-column unit at 0.855 and a 32-column unit at 0.63 of the pipe's "
+                                   "peak rate: 0.78 for the 3+2 unit mix; ncu: tensor pipe active 64 % of cycles",
                     "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops_sustained (8-bit operands run at twice the bf16 rate on "
                                     "the same pipe; tools/probe_umma.cu: 128 x 256 x 32 kind::i8 MMAs issue at exactly that rate)"
                                     if peaks else "2 x fallback 1400 TFLOP/s bf16 sustained"),
