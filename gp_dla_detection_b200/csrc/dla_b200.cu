@@ -264,6 +264,7 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
   namespace sl = dla::sl;
   const bool time_it = tev != nullptr;
   const int nsb = (int)((S + 1 + sl::SB - 1) / sl::SB);   // 128-sample blocks
+  const sl::SliceLayout L = sl::slice_layout(k);
   const bool ov = c->overlap;
   cudaStream_t sa = c->stream, sb = ov ? c->stream2 : c->stream;
   dla_ctx::SliceSet& set = c->sset[ov ? (c->slice_chunks & 1) : 0];
@@ -281,10 +282,10 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
     dla::pack_pixels_kernel<<<grid, 256, 0, sa>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, in.pix4);
     sl::pixel_scales_kernel<<<grid, 256, 0, sa>>>(in.desc, ch.q0, in.flux, in.mu, in.om, in.nv, c->d_isc.as<double2>(),
                                                   c->d_csc.as<double2>());
-    sl::table_colscale_kernel<<<dim3(sl::GCOLS, (unsigned)ch.nq), 128, 0, sa>>>(
-        in.desc, ch.q0, in.M, k, c->d_csc.as<double2>(), set.tau.as<double>(), set.colscale.as<double>());
-    sl::table_slices_kernel<<<dim3((unsigned)(2 * ch.max_nks), (unsigned)ch.nq), sl::GCOLS, 0, sa>>>(
-        in.desc, in.sq, ch.q0, in.M, k, c->d_csc.as<double2>(), set.tau.as<double>(), Bt);
+    sl::table_colscale_kernel<<<dim3((unsigned)L.gcols, (unsigned)ch.nq), 128, 0, sa>>>(
+        in.desc, ch.q0, in.M, L, c->d_csc.as<double2>(), set.tau.as<double>(), set.colscale.as<double>());
+    sl::table_slices_kernel<<<dim3((unsigned)((2 * ch.max_nks * L.gcols + 255) / 256), (unsigned)ch.nq), 256, 0, sa>>>(
+        in.desc, in.sq, ch.q0, in.M, L, c->d_csc.as<double2>(), set.tau.as<double>(), Bt);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[1], sa));
   const int nch = 2 * ch.max_nks;
@@ -312,17 +313,25 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
   if (time_it) CU_TRY(c, cudaEventRecord(tev[3], sb));
   {
     NvtxRange r("dla K2s tcgen05 contraction");
-    const int64_t ntiles = (int64_t)ch.nq * nsb * sl::UNITS;
+    const int64_t ntiles = (int64_t)ch.nq * nsb * L.nunits;
+    if (ntiles > (int64_t)INT32_MAX) BAD_ARG(c, "too many contraction tiles in one chunk");
     const unsigned grid = (unsigned)std::min<int64_t>(ntiles, c->num_sms);
-    launch_k2s(c->k2s_mode, ov ? 3 : c->k2s_stages, grid, sb, in.sq, ch.q0, ch.nq, nsb, (const int8_t*)Aw, (const int8_t*)Au,
+    launch_k2s(c->k2s_mode, ov ? 3 : c->k2s_stages, grid, sb, in.sq, ch.q0, ch.nq, nsb, L, (const int8_t*)Aw, (const int8_t*)Au,
                (const int8_t*)Bt, (const double*)set.colscale.as<double>(), G);
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[4], sb));
   {
     NvtxRange r("dla K2c cholesky + K3 reduce");
-    dim3 grid((unsigned)(nsb * (sl::SB / sl::K2C_ROWS)), (unsigned)ch.nq);
-    sl::chol_rows_kernel<<<grid, sl::K2C_ROWS * 4, sl::K2C_SMEM, sb>>>(in.desc, ch.q0, nsb, S, G, aux, d_perm, sample_ll_chunk,
-                                                                      ll_no, k, nseg);
+    if (k <= dla::KMAX) {
+      dim3 grid((unsigned)(nsb * (sl::SB / sl::K2C_ROWS)), (unsigned)ch.nq);
+      sl::chol_rows_kernel<<<grid, sl::K2C_ROWS * 4, sl::K2C_SMEM, sb>>>(in.desc, ch.q0, nsb, S, G, aux, d_perm, sample_ll_chunk,
+                                                                        ll_no, k, nseg);
+    } else {
+      // rows of G are [S_pad128][gcols]: the generic bordered Cholesky reads them with its 64-sample block count doubled
+      dim3 g2((unsigned)((S + 1 + dla::CHG_WARPS - 1) / dla::CHG_WARPS), (unsigned)ch.nq);
+      dla::chol_generic_kernel<<<g2, dla::CHG_WARPS * 32, dla::chg_smem_bytes(k), sb>>>(
+          in.desc, ch.q0, nsb * (sl::SB / dla::TS), S, G, aux, d_perm, sample_ll_chunk, ll_no, k, L.gcols, L.voff, nseg);
+    }
   }
   if (time_it) CU_TRY(c, cudaEventRecord(tev[5], sb));
   if (S > 0 && ll_dla) {
@@ -500,14 +509,15 @@ static int ensure_workspace(dla_ctx* c, int k, int64_t wu_doubles, int64_t bmat_
   CU_TRY(c, c->d_bmat.ensure((size_t)(bmat_doubles / dla::NCOL + 1) * gen.ncol * 8));
   CU_TRY(c, c->d_aux.ensure((size_t)nq * 2 * dla::K1S_NSEG_MAX * S_pad128 * 8));
   if (nq_slices > 0) {
-    CU_TRY(c, c->d_G.ensure((size_t)nq_slices * S_pad128 * dla::sl::GCOLS * 8));
+    const size_t gcols = (size_t)dla::sl::slice_layout(k).gcols;
+    CU_TRY(c, c->d_G.ensure((size_t)nq_slices * S_pad128 * gcols * 8));
     for (int i = 0; i < (c->overlap ? 2 : 1); ++i) {
       dla_ctx::SliceSet& set = c->sset[i];
       CU_TRY(c, set.W.ensure((size_t)std::max<int64_t>(a_bytes, 32)));
       CU_TRY(c, set.U.ensure((size_t)std::max<int64_t>(a_bytes, 32)));
       CU_TRY(c, set.btab.ensure((size_t)std::max<int64_t>(b_bytes, 32)));
-      CU_TRY(c, set.tau.ensure((size_t)nq_slices * dla::sl::GCOLS * 8));
-      CU_TRY(c, set.colscale.ensure((size_t)nq_slices * dla::sl::GCOLS * 8));
+      CU_TRY(c, set.tau.ensure((size_t)nq_slices * gcols * 8));
+      CU_TRY(c, set.colscale.ensure((size_t)nq_slices * gcols * 8));
       CU_TRY(c, set.aux.ensure((size_t)nq_slices * 2 * dla::K1S_NSEG_MAX * S_pad128 * 8));
     }
   }
@@ -860,10 +870,11 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
   // chunk plan: W+U of a chunk fit the workspace budget; at least a few chunks when the batch is
   // large enough, so that copies of one chunk overlap the kernels of another (dla_eval_batch)
   c->chunks.clear();
-  // exact-slice contraction: eligible batches (k <= 20, three lines) plan their chunks for either kernel family; a
+  // exact-slice contraction: eligible batches (three lines, any rank) plan their chunks for either kernel family; a
   // chunk takes the slice path when all of its quasars use the as-written gather
   namespace sl = dla::sl;
-  const bool slices_elig = c->use_slices && c->p.k <= dla::KMAX && c->p.num_lines == 3;
+  const bool slices_elig = c->use_slices && c->p.k <= dla::KGEN_MAX && c->p.num_lines == 3;
+  const int64_t sl_gcols = sl::slice_layout(c->p.k).gcols, sl_bqstep = (int64_t)sl::B_COLSTEP * sl_gcols;
   const int64_t S_pad128 = round_up(S + 1, sl::SB), nsb128 = S_pad128 / sl::SB;
   c->h_sq.assign((size_t)Q, SliceQuasar{});
   auto nks_of = [](const QuasarDesc& d) { return (int64_t)((std::max<int32_t>(d.n, 1) + sl::KS - 1) / sl::KS); };
@@ -871,9 +882,9 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
     long double b = 16.0L * S_pad * d.npad + gq;
     if (slices_elig) {
       // sample planes of W and U + table planes + partial sums, once per set; G once
-      const long double per_set = 2.0L * nsb128 * nks_of(d) * sl::A_STEP7 + (long double)nks_of(d) * sl::B_QSTEP +
+      const long double per_set = 2.0L * nsb128 * nks_of(d) * sl::A_STEP7 + (long double)nks_of(d) * sl_bqstep +
                                   16.0L * dla::K1S_NSEG_MAX * S_pad128;
-      b = std::max(b, (c->overlap ? 2 : 1) * per_set + 8.0L * S_pad128 * sl::GCOLS);
+      b = std::max(b, (c->overlap ? 2 : 1) * per_set + 8.0L * S_pad128 * sl_gcols);
     }
     return b;
   };
@@ -925,7 +936,7 @@ static int plan_batch(dla_ctx* c, int64_t Q, const int64_t* pix_ptr, const int64
         sq.a_off = ch.a_bytes;
         sq.b_off = ch.b_bytes;
         ch.a_bytes += nsb128 * sq.nks * sl::A_STEP7;
-        ch.b_bytes += (int64_t)sq.nks * sl::B_QSTEP;
+        ch.b_bytes += (int64_t)sq.nks * sl_bqstep;
         ch.max_nks = std::max(ch.max_nks, (int)sq.nks);
         acc += bts;
         ++ch.nq;

@@ -1,6 +1,6 @@
 // slices_path.cuh -- the product path of the exact-slice int8 contraction (primitives: slices.cuh).
 //
-// For k <= 20, three lines and the as-written gather, the Woodbury contraction of log_mvnpdf_low_rank.m:22 and
+// For three lines and the as-written gather (any rank k <= 64), the Woodbury contraction of log_mvnpdf_low_rank.m:22 and
 // :26-28 leaves the FP64 pipe: the Voigt kernel emits W and U directly as seven signed 8-bit slices per value
 // (same bytes as fp64, minus one), the per-quasar table [Phi | M] is sliced once, and the products run on the
 // integer tcgen05 path with int32 TMEM accumulators, one per slice diagonal.  Pipeline of a chunk of quasars:
@@ -11,7 +11,8 @@
 //   voigt_slices_lane_kernel voigt.c:278-299 + process_qsos.m:189-193 -> int8 planes of W / c_w, U / c_u,
 //                            partial sums of r'D^-1 r and log|D| (fp64)                            (K1s)
 //   contract_slices_tiles_kernel   G = [W | U] . [Phi | M] on kind::i8 tcgen05, fp64 recombination  (K2s)
-//   chol_rows_kernel         per-sample bordered 21 x 21 Cholesky (registers, one quad per sample)  (K2c)
+//   chol_rows_kernel         per-sample bordered 21 x 21 Cholesky (registers, one quad per sample)  (K2c, k <= 20)
+//   chol_generic_kernel      the same for 20 < k <= 64 from the rows of G (kernels.cuh: shared memory, warp per sample)
 //
 // Fixed point.  Sample side: t = w / c_w in [0, 1) or t = u / c_u in (-1/2, 1/2) enters a double's mantissa by ONE
 // fma with a magic constant (1.0 / 1.5): X = round(t 2^52), two's complement.  Its bytes ARE the slices: X = a_0 256^6
@@ -32,10 +33,50 @@ constexpr int NSL = 7;                         // slices per value
 constexpr int A_STEP7 = NSL * 2 * SB * 16;     // 28 672 bytes of sample planes per K step (32 pixels, 128 samples)
 constexpr int B_STEP64 = NSL * 2 * 64 * 16;    // 14 336 bytes of table planes per K step, 64-column unit
 constexpr int B_STEP32 = NSL * 2 * 32 * 16;    //  7 168, 32-column unit
-constexpr int B_QSTEP = 3 * B_STEP64 + 2 * B_STEP32;   // table bytes per K step and quasar: 57 344
 constexpr int GCOLS = 256;                     // row of G: [0, 224) W.Phi (k (k+1) / 2 used), [224, 256) U.M (k used)
 constexpr int VOFF_S = 224;
 constexpr int UNITS = 5;                       // column units per sample block: 64, 64, 64, 32 (W planes), 32 (U planes)
+constexpr int B_COLSTEP = NSL * 2 * 16;        // 224 table bytes per K step and column
+// Column layout of a row of G for rank k.  A segment of C columns (C = k (k + 1) / 2 for W.Phi, C = k for U.M) is cut
+// into floor(C / 64) units of 64 columns and, for the rest r, one more unit of 64 (r > 32) or 32 (r > 0) columns.
+// k <= 20 keeps the fixed layout above (64, 64, 64, 32 | 32: what chol_rows_kernel reads); k = 40: 13 x 64 | 64.
+// Unit u starts at column col0(u) of the row AND at byte nks * 224 * col0(u) of the quasar's table planes.
+struct SliceLayout {
+  int k, T;        // rank, k (k + 1) / 2
+  int voff;        // first U.M column = padded width of the W.Phi segment
+  int gcols;       // row length of G, tau and colscale
+  int nunits, nwu; // units per sample block; the first nwu read the W planes
+  int w64, u64;    // 64-column units of the two segments (the 32-column one, if any, is the segment's last)
+};
+__host__ __device__ inline SliceLayout slice_layout(int k) {
+  SliceLayout L;
+  L.k = k;
+  L.T = k * (k + 1) / 2;
+  if (k <= 20) {
+    L.voff = VOFF_S; L.gcols = GCOLS; L.nunits = UNITS; L.nwu = 4; L.w64 = 3; L.u64 = 0;
+    return L;
+  }
+  int r = L.T % 64;
+  L.w64 = L.T / 64 + (r > 32 ? 1 : 0);
+  if (r > 32) r = 0;
+  L.nwu = L.w64 + (r > 0 ? 1 : 0);
+  L.voff = 64 * L.w64 + (r > 0 ? 32 : 0);
+  r = k % 64;
+  L.u64 = k / 64 + (r > 32 ? 1 : 0);
+  if (r > 32) r = 0;
+  L.nunits = L.nwu + L.u64 + (r > 0 ? 1 : 0);
+  L.gcols = L.voff + 64 * L.u64 + (r > 0 ? 32 : 0);
+  return L;
+}
+// unit that holds column c: its first column and width
+__host__ __device__ inline void unit_of_col(const SliceLayout& L, int c, int& col0, int& N) {
+  if (c < L.voff) {
+    if (c < 64 * L.w64) { col0 = c & ~63; N = 64; } else { col0 = 64 * L.w64; N = 32; }
+  } else {
+    const int cu = c - L.voff;
+    if (cu < 64 * L.u64) { col0 = L.voff + (cu & ~63); N = 64; } else { col0 = L.voff + 64 * L.u64; N = 32; }
+  }
+}
 constexpr int K2S_STAGE = A_STEP7 + B_STEP64;  // 43 008
 // ring depth of the contraction: 5 when it has the SM to itself, 3 (130 KB) when Voigt CTAs of the next chunk share it
 constexpr size_t k2s_smem(int stages) { return (size_t)stages * K2S_STAGE + 1024 + 256; }
@@ -100,16 +141,17 @@ __global__ void pixel_scales_kernel(const QuasarDesc* __restrict__ desc, int q0,
 }
 
 // table entry of column c (0 <= c < 256) at pixel p, scaled by the pixel's power of two
-__device__ __forceinline__ void col_to_il(int c, int k, int& i, int& l) {
+__device__ __forceinline__ void col_to_il(int c, const SliceLayout& L, int& i, int& l) {
+  const int k = L.k;
   i = -1;
   l = -1;
-  if (c < k * (k + 1) / 2) {
+  if (c < L.T) {
     i = (int)((sqrt(8.0 * c + 1.0) - 1.0) * 0.5);
     while (i * (i + 1) / 2 > c) --i;
     while ((i + 1) * (i + 2) / 2 <= c) ++i;
     l = c - i * (i + 1) / 2;
-  } else if (c >= VOFF_S && c < VOFF_S + k) {
-    i = c - VOFF_S;
+  } else if (c >= L.voff && c < L.voff + k) {
+    i = c - L.voff;
   }
 }
 __device__ __forceinline__ double table_entry(const double* __restrict__ Mq, int n, int p, int i, int l, double2 cs) {
@@ -118,13 +160,13 @@ __device__ __forceinline__ double table_entry(const double* __restrict__ Mq, int
 }
 // column scales: tau_c = 2^ceil(log2 max_p |entry|) (1 for an empty column, NaN if any entry is NaN: a NaN model
 // entry must poison every sample of the quasar as it does in fp64); colscale = tau 2^-10
-__global__ void table_colscale_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ M, int k,
+__global__ void table_colscale_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ M, SliceLayout L,
                                       const double2* __restrict__ csc, double* __restrict__ tau,
                                       double* __restrict__ colscale) {
   const QuasarDesc d = desc[q0 + blockIdx.y];
-  const int c = blockIdx.x;
+  const int c = blockIdx.x, k = L.k;
   int i, l;
-  col_to_il(c, k, i, l);
+  col_to_il(c, L, i, l);
   __shared__ double red[128];
   double m = 0.0;
   bool bad = false;
@@ -156,26 +198,26 @@ __global__ void table_colscale_kernel(const QuasarDesc* __restrict__ desc, int q
       t = ldexp(1.0, (f == 0.5) ? e - 1 : e);
       if (!(t < 1.7e308)) t = qnan;   // an infinite entry: poison
     }
-    tau[(int64_t)blockIdx.y * GCOLS + c] = t;
-    colscale[(int64_t)blockIdx.y * GCOLS + c] = t * 0.0009765625;
+    tau[(int64_t)blockIdx.y * L.gcols + c] = t;
+    colscale[(int64_t)blockIdx.y * L.gcols + c] = t * 0.0009765625;
   }
 }
-// planes: unit u < 3: [K step][2][slice][64 columns][16 B] at b_off + u nks B_STEP64; u = 3, 4: 32 columns, at
-// b_off + 3 nks B_STEP64 + (u - 3) nks B_STEP32.  Within a 16-byte K chunk the slices are stacked like extra columns
+// planes of a unit of N columns starting at column col0: [K step][2][slice][N columns][16 B] at b_off + nks 224 col0
+// (k <= 20: units 0..2 at u nks B_STEP64, units 3 and 4 of 32 columns behind them).  Within a 16-byte K chunk the slices are stacked like extra columns
 // (row j N + c of the operand = slice j, column c), so that ONE MMA multiplies a sample slice with several table
 // slices at once.  One thread per (column, 16-pixel chunk); pixels >= n are zero.
 __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar* __restrict__ sq, int q0,
-                                    const double* __restrict__ M, int k, const double2* __restrict__ csc,
+                                    const double* __restrict__ M, SliceLayout L, const double2* __restrict__ csc,
                                     const double* __restrict__ tau, int8_t* __restrict__ planes) {
   const QuasarDesc d = desc[q0 + blockIdx.y];
   const SliceQuasar s = sq[q0 + blockIdx.y];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const int nch = s.nks * 2;
-  if (idx >= GCOLS * nch) return;
-  const int col = idx % GCOLS, ch = idx / GCOLS;   // consecutive threads = consecutive columns (contiguous 16-byte pieces)
+  const int nch = s.nks * 2, k = L.k;
+  if (idx >= L.gcols * nch) return;
+  const int col = idx % L.gcols, ch = idx / L.gcols;   // consecutive threads = consecutive columns (contiguous 16-byte pieces)
   int i, l;
-  col_to_il(col, k, i, l);
-  const double tc = tau[(int64_t)blockIdx.y * GCOLS + col];
+  col_to_il(col, L, i, l);
+  const double tc = tau[(int64_t)blockIdx.y * L.gcols + col];
   const double it = 1.0 / tc;   // a power of two; NaN -> zeros here, the NaN travels in colscale
   const double* Mq = M + (int64_t)k * d.pix_off;
   uint64_t dig[16];
@@ -186,10 +228,10 @@ __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const S
     if (i >= 0 && px < d.n) v = table_entry(Mq, d.n, px, i, l, csc[d.pix_off + px]) * it;
     dig[p] = balanced_digits<NSL>(to_fixed<NSL>(v == v ? v : 0.0));
   }
-  const int u = (col < 192) ? (col >> 6) : (col < VOFF_S ? 3 : 4);
-  const int N = (u < 3) ? 64 : 32;
-  const int cc = (u < 3) ? (col & 63) : (col & 31);
-  const int64_t ubase = (u < 3) ? (int64_t)u * s.nks * B_STEP64 : (int64_t)3 * s.nks * B_STEP64 + (int64_t)(u - 3) * s.nks * B_STEP32;
+  int col0, N;
+  unit_of_col(L, col, col0, N);
+  const int cc = col - col0;
+  const int64_t ubase = (int64_t)s.nks * B_COLSTEP * col0;
   const int ks = ch >> 1, c2 = ch & 1;
   int8_t* base = planes + s.b_off + ubase + (int64_t)ks * (NSL * 2 * N * 16) + (int64_t)c2 * (NSL * N * 16) + cc * 16;
 #pragma unroll
@@ -380,20 +422,22 @@ struct K2sTile {
   const int8_t* b;
   int nks, N, ql, sb, col0;
 };
-__device__ __forceinline__ K2sTile k2s_decode(int t, const SliceQuasar* __restrict__ sq, int q0, int nsb, const int8_t* Aw,
-                                              const int8_t* Au, const int8_t* Bt) {
+__device__ __forceinline__ K2sTile k2s_decode(int t, const SliceQuasar* __restrict__ sq, int q0, int nsb, const SliceLayout& L,
+                                              const int8_t* Aw, const int8_t* Au, const int8_t* Bt) {
   K2sTile r;
-  const int per = nsb * UNITS;
+  const int per = nsb * L.nunits;
   r.ql = t / per;
   const int rem = t - r.ql * per;
-  r.sb = rem / UNITS;
-  const int u = rem - r.sb * UNITS;
+  r.sb = rem / L.nunits;
+  const int u = rem - r.sb * L.nunits;
   const SliceQuasar s = sq[q0 + r.ql];
   r.nks = s.nks;
-  r.N = (u < 3) ? 64 : 32;
-  r.col0 = (u < 3) ? 64 * u : (u == 3 ? 192 : VOFF_S);
-  r.a = ((u == 4) ? Au : Aw) + s.a_off + (int64_t)r.sb * s.nks * A_STEP7;
-  r.b = Bt + s.b_off + ((u < 3) ? (int64_t)u * s.nks * B_STEP64 : (int64_t)3 * s.nks * B_STEP64 + (int64_t)(u - 3) * s.nks * B_STEP32);
+  const bool isu = u >= L.nwu;
+  const int uu = isu ? u - L.nwu : u, n64 = isu ? L.u64 : L.w64;
+  r.N = (uu < n64) ? 64 : 32;
+  r.col0 = (isu ? L.voff : 0) + 64 * ((uu < n64) ? uu : n64);
+  r.a = (isu ? Au : Aw) + s.a_off + (int64_t)r.sb * s.nks * A_STEP7;
+  r.b = Bt + s.b_off + (int64_t)s.nks * B_COLSTEP * r.col0;
   return r;
 }
 
@@ -428,7 +472,7 @@ __device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, u
 // launch bounds: the second number only caps the registers (shared memory allows one CTA per SM anyway)
 template <int MODE, int K2S_STAGES>
 __global__ void __launch_bounds__(K2S_THREADS, 2)
-contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq, int nsb, const int8_t* __restrict__ Aw,
+contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq, int nsb, const SliceLayout L, const int8_t* __restrict__ Aw,
                              const int8_t* __restrict__ Au, const int8_t* __restrict__ Bt, const double* __restrict__ colscale,
                              double* __restrict__ G) {
   extern __shared__ unsigned char sl_smem_raw[];
@@ -439,7 +483,7 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
   uint64_t* tempty = tfull + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int ntiles = nq * nsb * UNITS;
+  const int ntiles = nq * nsb * L.nunits;
   const bool tracing = g_trace != nullptr;
   const unsigned long long trace_t0 = (tracing && tid == 0) ? trace_now() : 0ull;
 
@@ -465,7 +509,7 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
     if (lane == 0) {
       uint32_t it = 0;
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const K2sTile tl = k2s_decode(t, sq, q0, nsb, Aw, Au, Bt);
+        const K2sTile tl = k2s_decode(t, sq, q0, nsb, L, Aw, Au, Bt);
         const uint32_t bstep = (uint32_t)(NSL * 2 * 16) * tl.N;
         for (int ks = 0; ks < tl.nks; ++ks, ++it) {
           const int st = it % K2S_STAGES;
@@ -484,7 +528,7 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
   } else if (warp == 1) {
     uint32_t it = 0, tcount = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
-      const K2sTile tl = k2s_decode(t, sq, q0, nsb, Aw, Au, Bt);
+      const K2sTile tl = k2s_decode(t, sq, q0, nsb, L, Aw, Au, Bt);
       bar_wait(tempty, (tcount & 1) ^ 1);   // the epilogue has drained the previous tile's accumulators
       tc_fence_after();
       for (int ks = 0; ks < tl.nks; ++ks, ++it) {
@@ -514,11 +558,11 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
     const int64_t S_pad = (int64_t)nsb * SB;
     uint32_t tcount = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tcount) {
-      const K2sTile tl = k2s_decode(t, sq, q0, nsb, Aw, Au, Bt);
+      const K2sTile tl = k2s_decode(t, sq, q0, nsb, L, Aw, Au, Bt);
       bar_wait(tfull, tcount & 1);
       tc_fence_after();
-      double* grow = G + ((int64_t)tl.ql * S_pad + (int64_t)tl.sb * SB + row) * GCOLS + tl.col0;
-      const double* cs = colscale + (int64_t)tl.ql * GCOLS + tl.col0;
+      double* grow = G + ((int64_t)tl.ql * S_pad + (int64_t)tl.sb * SB + row) * L.gcols + tl.col0;
+      const double* cs = colscale + (int64_t)tl.ql * L.gcols + tl.col0;
       const int nc8h = tl.N / 16;
 #pragma unroll 1
       for (int c8 = half * nc8h; c8 < (half + 1) * nc8h; ++c8) {

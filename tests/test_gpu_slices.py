@@ -1,4 +1,4 @@
-"""-m gpu: the exact-slice int8 tcgen05 contraction (csrc/slices_path.cuh), the default path for k <= 20, three lines
+"""-m gpu: the exact-slice int8 tcgen05 contraction (csrc/slices_path.cuh), the default path for three lines
 and the as-written gather (log_mvnpdf_low_rank.m:22, :26-28 off the FP64 pipe).
 
   * it IS the path that runs (dla_timing.contraction == 1) and it meets the north_star gates against the C oracle
@@ -7,7 +7,8 @@ and the as-written gather (log_mvnpdf_low_rank.m:22, :26-28 off the FP64 pipe).
   * a quasar with huge dynamic range of the noise variance (per-pixel power-of-two scales, column scales)
   * NaN inputs poison exactly what they poison in fp64
   * chunked and overlapped schedules give bit-identical results
-  * batches the slice path must not take (masked gather, num_lines != 3, k > 20) fall back to the DMMA kernels
+  * any rank 1 <= k <= 64 (column-unit layouts), BASELINE config 5 (k = 40)
+  * batches the slice path must not take (masked gather, num_lines != 3) fall back to the DMMA kernels
 All through the C ABI.
 """
 import copy
@@ -140,8 +141,9 @@ def test_voigt_kernel_builds(oracle, monkeypatch, variant):
     assert_parity(got, ref)
 
 
-def test_fallbacks_to_the_dmma_kernels(oracle):
-    """Masked gather, num_lines != 3 and k > 20 are not slice-path batches: the FP64 kernels run them."""
+def test_fallbacks_to_the_dmma_kernels(oracle, monkeypatch):
+    """Masked gather and num_lines != 3 are not slice-path batches: the FP64 kernels run them; so does any batch
+    under DLA_B200_CONTRACT=dmma (k = 40: column-block DMMA contraction + shared-memory Cholesky)."""
     S = 200
     params, model, samples, sp, prepared = prepared_config("config3", 3, S, "intended")
     got = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla)
@@ -150,7 +152,44 @@ def test_fallbacks_to_the_dmma_kernels(oracle):
     got = _run(prepared, samples, 20, S, sp.log_priors_dla, sp.log_priors_no_dla, num_lines=5)
     assert got["_timing"]["contraction"] == 0
     params, model, samples, sp, prepared = prepared_config("config5", 2, S)
+    monkeypatch.setenv("DLA_B200_CONTRACT", "dmma")
     got = _run(prepared, samples, 40, S, sp.log_priors_dla, sp.log_priors_no_dla)
     assert got["_timing"]["contraction"] == 0
     ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(got, ref)
+
+
+def test_rank40_config5_takes_the_slice_path(oracle, monkeypatch):
+    """BASELINE config 5 (k = 40, 2433 px): 13 + 1 column units of 64, rows of G 896 wide, generic bordered Cholesky."""
+    S = 300
+    params, model, samples, sp, prepared = prepared_config("config5", 3, S)
+    got = _run(prepared, samples, 40, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 1
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    worst = assert_parity(got, ref)
+    monkeypatch.setenv("DLA_B200_CONTRACT", "dmma")
+    dmma = _run(prepared, samples, 40, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    both = float(np.max(np.abs(got["sample_log_likelihoods_dla"] - dmma["sample_log_likelihoods_dla"])))
+    print(f"k = 40: slices vs oracle worst rel {worst:.2e}; slices vs DMMA worst abs {both:.2e}")
+    assert both <= 5e-9
+    assert np.array_equal(got["map_ind"], dmma["map_ind"])
+
+
+@pytest.mark.parametrize("k", [1, 7, 21, 32, 33, 45, 64])
+def test_any_rank_on_the_slice_path(oracle, k):
+    """Column-unit layouts of every kind: k <= 20 fixed layout; k = 21 (231 = 3 x 64 + 39 -> four 64-units | 32),
+    32 (528 = 8 x 64 + 16 -> a 32-unit | 32), 33 (561 -> 49 left: ninth 64-unit | 64), 45 (1035 -> 11 left: 32-unit | 64),
+    64 (2080 = 32 x 64 + 32 -> 32-unit | 64)."""
+    S = 200
+    params, model, samples, sp, prepared = prepared_config("config3", 3, S)
+    rng = np.random.default_rng(100 + k)
+    mine = []
+    for p in prepared:
+        p = copy.deepcopy(p)
+        n = p.flux.shape[0]
+        p.M = np.asfortranarray(rng.normal(size=(n, k)) * (0.4 / np.sqrt(k)) * (1 + np.arange(k)) ** -0.3)
+        mine.append(p)
+    got = _run(mine, samples, k, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 1
+    ref = oracle_batch(oracle, mine, samples, sp.log_priors_dla, sp.log_priors_no_dla)
     assert_parity(got, ref)
