@@ -5,11 +5,15 @@
   preloaded_qsos.mat           preload_qsos.m:73-79         -> load_preloaded_qsos
   processed_qsos_<set>.mat     process_qsos.m:235-249       -> save_processed_qsos / load_processed_qsos
 
-The reference writes MATLAB v7.3 files (= HDF5).  Reading/writing HDF5 needs h5py, which is NOT in
-this image; when it is importable the v7.3 branch is used (datasets are stored transposed, ragged cell
-arrays as object references: the conventions CDDF_analysis/calc_cddf.py:59-124 relies on).  Without
-h5py the same variables are exchanged as MATLAB v5/v7 files through scipy.io (both MATLAB and Octave
-load them with a plain ``load``), which is also what the tests exercise here.
+The reference writes MATLAB v7.3 files (= HDF5; process_qsos.m:249, because sample_log_likelihoods_dla is
+[num_quasars x 10000] doubles: 13 GB for DR12Q).  There is no h5py in this image, so the subset of HDF5 these
+files need is written and read by hdf5_min.py (numpy + struct: contiguous little-endian datasets, MATLAB's
+transposed layout, MATLAB_class attributes, cell arrays as object references -- the conventions
+CDDF_analysis/calc_cddf.py:59-124 relies on).  save_processed_qsos writes v7.3 by default, as the reference does.
+Reading MATLAB-WRITTEN v7.3 files whose variables are chunked / compressed (MATLAB's default for large arrays):
+needs h5py, unavailable on this box -- hdf5_min says so when it meets one, and h5py is used when importable.
+The v5 / v7 format (scipy.io; plain ``load`` in MATLAB and Octave) remains for small files and cannot hold a
+variable of 2 GiB or more: asking for it with such a result is an error, not a silent truncation.
 """
 from __future__ import annotations
 
@@ -32,9 +36,11 @@ def _h5py():
     try:
         import h5py  # noqa: F401
         return h5py
-    except ImportError as e:
-        raise ImportError("this file is MATLAB v7.3 (HDF5); reading it needs h5py, which is not installed. "
-                          "Re-save it from MATLAB/Octave with `save -v7 ...` or install h5py.") from e
+    except ImportError:
+        return None
+
+
+V5_LIMIT_BYTES = 2 ** 31 - 8   # a MATLAB v5 / v7 data element carries a 32-bit byte count
 
 
 def _load(path: str, names) -> dict:
@@ -42,6 +48,14 @@ def _load(path: str, names) -> dict:
     if _is_hdf5(path):
         h5py = _h5py()
         out = {}
+        if h5py is None:
+            from . import hdf5_min
+            with hdf5_min.File(path) as f:
+                for n in names:
+                    if n not in f.members:
+                        raise KeyError(f"{path}: no variable {n!r}")
+                    out[n] = f.read(n)
+            return out
         with h5py.File(path, "r") as f:
             for n in names:
                 ds = f[n]
@@ -85,10 +99,12 @@ def load_preloaded_qsos(path: str) -> dict:
     return v
 
 
-def save_processed_qsos(path: str, results: dict, extra: dict | None = None, v73: bool = False) -> None:
+def save_processed_qsos(path: str, results: dict, extra: dict | None = None, v73: bool = True) -> None:
     """processed_qsos_<set>.mat with the variables of process_qsos.m:235-243 (column vectors, [Q x S]
     sample matrix, [Q x 2] posteriors).  ``extra``: the bookkeeping variables of :235-238 (release names,
-    test_ind, ...).  v73=True writes HDF5 with MATLAB's transposed layout (needs h5py)."""
+    test_ind, ...).  v73=True (default, as process_qsos.m:249): HDF5 with MATLAB's transposed layout and
+    MATLAB_class attributes, streamed by hdf5_min (no h5py needed).  v73=False: MATLAB v5 through scipy.io;
+    raises when a variable does not fit that format."""
     vars_ = {}
     for n in RESULT_VARIABLES:
         if results.get(n) is None:
@@ -98,13 +114,14 @@ def save_processed_qsos(path: str, results: dict, extra: dict | None = None, v73
     for n, a in (extra or {}).items():
         vars_[n] = a
     if v73:
-        h5py = _h5py()
-        with h5py.File(path, "w", userblock_size=512) as f:
-            for n, a in vars_.items():
-                f.create_dataset(n, data=np.asarray(a).T)
-        with open(path, "r+b") as f:  # the v7.3 text header MATLAB looks for
-            f.write(b"MATLAB 7.3 MAT-file, Platform: gp_dla_detection_b200".ljust(124) + b"\x00\x02IM")
+        from . import hdf5_min
+        hdf5_min.write(path, vars_)
         return
+    for n, a in vars_.items():
+        nbytes = np.asarray(a).nbytes if not isinstance(a, str) else len(a)
+        if nbytes > V5_LIMIT_BYTES:
+            raise ValueError(f"{n} is {nbytes} bytes: a MATLAB v5 file cannot hold it; save with v73=True "
+                             f"(the reference's own format, process_qsos.m:249)")
     from scipy.io import savemat
     savemat(path, vars_, do_compression=False, oned_as="column")
 

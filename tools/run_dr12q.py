@@ -27,6 +27,9 @@ def main():
     ap.add_argument("--samples", type=int, default=10000)
     ap.add_argument("--no-sample-ll", action="store_true", help="do not bring sample_log_likelihoods_dla back")
     ap.add_argument("--repeat", action="store_true", help="time a second identical call as well (buffers already sized)")
+    ap.add_argument("--save", default=None, metavar="DIR",
+                    help="write each rank's shard as DIR/processed_qsos_dr12q_rank<r>.mat (MATLAB v7.3 = HDF5, "
+                         "process_qsos.m:245-249) through mat_io.save_processed_qsos and read one variable back")
     args = ap.parse_args()
 
     import torch
@@ -124,6 +127,25 @@ def main():
         ok = ok and bool(np.array_equal(out["map_ind"][sub], np.argmax(ll[sub], axis=1)))
     n_dla = int(np.sum(out["log_posteriors_dla"] > out["log_posteriors_no_dla"]))
     inj = int(np.sum(sp.injected))
+    save_s = save_bytes = None
+    if args.save:
+        from gp_dla_detection_b200 import mat_io
+        os.makedirs(args.save, exist_ok=True)
+        path = os.path.join(args.save, f"processed_qsos_dr12q_rank{rank}.mat")
+        res = dict(out)
+        res["log_priors_dla"], res["log_priors_no_dla"] = sp.log_priors_dla, sp.log_priors_no_dla
+        res["p_no_dlas"] = out["model_posteriors"][:, 0]                       # process_qsos.m:231
+        res["p_dlas"] = 1 - res["p_no_dlas"]                                   # :232
+        t0 = time.perf_counter()
+        mat_io.save_processed_qsos(path, res, extra={"test_set_name": "dr12q_synthetic", "num_lines": 3,
+                                                     "max_z_cut": params.max_z_cut, "min_z_cut": params.min_z_cut})
+        save_s = time.perf_counter() - t0
+        save_bytes = os.path.getsize(path)
+        back = mat_io.load_processed_qsos(path)
+        ok = ok and bool(np.array_equal(back["log_posteriors_dla"], out["log_posteriors_dla"]))
+        if out["sample_log_likelihoods_dla"] is not None:
+            ok = ok and bool(np.array_equal(back["sample_log_likelihoods_dla"][::97], out["sample_log_likelihoods_dla"][::97]))
+        del back
 
     wall_max = reduce(wall, "MAX")
     total_q = int(round(reduce(float(nq), "SUM")))
@@ -134,6 +156,8 @@ def main():
     d2h = reduce(float(tm["d2h_bytes"]), "SUM")
     gen_max = reduce(t_gen, "MAX")
     wall2_max = reduce(wall2, "MAX") if args.repeat else None
+    if args.save:
+        save_max, save_total = reduce(save_s, "MAX"), reduce(float(save_bytes), "SUM")
     if rank == 0:
         print(json.dumps({
             "workload": "BASELINE config 2 at full size: %d distinct synthetic quasars x %d hypotheses, k=20, 1217 px" % (total_q, S),
@@ -145,6 +169,9 @@ def main():
             "device_ms_sum_over_chunks_rank0": {k: tm[k] for k in ("ms_total", "ms_voigt", "ms_contract", "ms_phi", "ms_reduce")},
             "second_call_seconds": wall2_max,
             "checks_passed": all_ok, "dla_decisions": n_dla, "injected_dlas": inj,
+            "saved": ({"format": "MATLAB v7.3 (HDF5) via mat_io.save_processed_qsos / hdf5_min, one file per rank",
+                       "seconds_max_over_ranks": save_max, "bytes_total": save_total, "read_back_equal": all_ok} if args.save else
+                      "outputs not written to disk in this run (--save DIR writes processed_qsos v7.3 files)"),
             "generation_seconds_outside_timed_region": gen_max}))
     if dist is not None:
         dist.destroy_process_group()
