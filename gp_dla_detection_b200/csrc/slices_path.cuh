@@ -15,12 +15,15 @@
 //   chol_generic_kernel      the same for 20 < k <= 64 from the rows of G (kernels.cuh: shared memory, warp per sample)
 //
 // Fixed point.  Sample side: t = w / c_w in [0, 1) or t = u / c_u in (-1/2, 1/2) enters a double's mantissa by ONE
-// fma with a magic constant (1.0 / 1.5): X = round(t 2^52), two's complement.  Its bytes ARE the slices: X = a_0 256^6
-// + sum_{i>=1} a_i 256^(6-i) with a_0 the signed top byte and a_1..a_6 plain unsigned bytes (the MMAs of slice 0 declare
-// a signed A operand, the others an unsigned one), so t = sum_i a_i 2^(-8 i - 4) with no digit arithmetic at all.
+// fma with a magic constant (1.0 / 1.5): X = round(t 2^52), two's complement.  The bytes of 16 X ARE the slices (a
+// funnel shift by four bits, so that the top slice carries eight significant bits instead of four and every kept slice
+// pair sits 16 x lower): 16 X = sum_i a_i 256^(6-i), a_1..a_6 plain unsigned bytes, a_0 the top byte -- unsigned for W
+// (t >= 0), signed for U; the MMAs of slice 0 of a U unit declare a signed A operand, all others an unsigned one.  So
+// t = sum_i a_i 2^(-8 i - 8) with no digit arithmetic at all.
 // Table side: b = entry / tau in [-1, 1] with 54 fractional bits in balanced digits b_j in [-128, 127],
-// b = sum_j b_j 2^(-8 j - 6).  Slice products with i + j = d share the weight 2^(-8 d - 10) and accumulate exactly
-// in int32 (|sum| <= 7 * 2^15 * pixels < 2^31 for pixels <= 9 000); pairs with i + j >= 7 are dropped.
+// b = sum_j b_j 2^(-8 j - 6).  Slice products with i + j = d share the weight 2^(-8 d - 14) and accumulate exactly
+// in int32 (|sum| <= 7 * 2^15 * pixels < 2^31 for pixels <= 9 000); pairs with i + j >= 7 are dropped: at most
+// 6 * 2^-55 of the product of the two scales per pixel, rms 2^-55 -- below the 2^-53 rounding of the sample value itself.
 #ifndef GPDLA_SLICES_PATH_CUH
 #define GPDLA_SLICES_PATH_CUH
 
@@ -159,7 +162,7 @@ __device__ __forceinline__ double table_entry(const double* __restrict__ Mq, int
   return (l >= 0) ? (mi * Mq[(int64_t)l * n + p]) * cs.x : mi * cs.y;
 }
 // column scales: tau_c = 2^ceil(log2 max_p |entry|) (1 for an empty column, NaN if any entry is NaN: a NaN model
-// entry must poison every sample of the quasar as it does in fp64); colscale = tau 2^-10
+// entry must poison every sample of the quasar as it does in fp64); colscale = tau 2^-14
 __global__ void table_colscale_kernel(const QuasarDesc* __restrict__ desc, int q0, const double* __restrict__ M, SliceLayout L,
                                       const double2* __restrict__ csc, double* __restrict__ tau,
                                       double* __restrict__ colscale) {
@@ -199,7 +202,7 @@ __global__ void table_colscale_kernel(const QuasarDesc* __restrict__ desc, int q
       if (!(t < 1.7e308)) t = qnan;   // an infinite entry: poison
     }
     tau[(int64_t)blockIdx.y * L.gcols + c] = t;
-    colscale[(int64_t)blockIdx.y * L.gcols + c] = t * 0.0009765625;
+    colscale[(int64_t)blockIdx.y * L.gcols + c] = t * 6.103515625e-05;
   }
 }
 // planes of a unit of N columns starting at column col0: [K step][2][slice][N columns][16 B] at b_off + nks 224 col0
@@ -263,8 +266,9 @@ __device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NS
   uint32_t lo[4], hi[4];
 #pragma unroll
   for (int h = 0; h < 4; ++h) {
-    lo[h] = (uint32_t)__double2loint(m[h]);
-    hi[h] = (uint32_t)__double2hiint(m[h]) - MAGIC_HI;
+    const uint32_t l = (uint32_t)__double2loint(m[h]), hh = (uint32_t)__double2hiint(m[h]) - MAGIC_HI;
+    lo[h] = l << 4;                         // 16 X: the top slice becomes bits 44..51 of X
+    hi[h] = __funnelshift_l(l, hh, 4);
   }
   const uint32_t t0 = __byte_perm(lo[0], lo[1], 0x5140), t1 = __byte_perm(lo[2], lo[3], 0x5140);
   const uint32_t t2 = __byte_perm(lo[0], lo[1], 0x7362), t3 = __byte_perm(lo[2], lo[3], 0x7362);
@@ -421,6 +425,7 @@ struct K2sTile {
   const int8_t* a;
   const int8_t* b;
   int nks, N, ql, sb, col0;
+  uint32_t isu;   // the unit reads the U planes (top slice signed)
 };
 __device__ __forceinline__ K2sTile k2s_decode(int t, const SliceQuasar* __restrict__ sq, int q0, int nsb, const SliceLayout& L,
                                               const int8_t* Aw, const int8_t* Au, const int8_t* Bt) {
@@ -435,6 +440,7 @@ __device__ __forceinline__ K2sTile k2s_decode(int t, const SliceQuasar* __restri
   const bool isu = u >= L.nwu;
   const int uu = isu ? u - L.nwu : u, n64 = isu ? L.u64 : L.w64;
   r.N = (uu < n64) ? 64 : 32;
+  r.isu = isu ? 1u : 0u;
   r.col0 = (isu ? L.voff : 0) + 64 * ((uu < n64) ? uu : n64);
   r.a = (isu ? Au : Aw) + s.a_off + (int64_t)r.sb * s.nks * A_STEP7;
   r.b = Bt + s.b_off + (int64_t)s.nks * B_COLSTEP * r.col0;
@@ -451,7 +457,7 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 template <int N>
-__device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, uint32_t tmem_base, uint32_t first) {
+__device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, uint32_t tmem_base, uint32_t first, uint32_t top_signed) {
   constexpr uint64_t HI = (uint64_t)(((128u >> 4) & 0x3FFFu) | (1u << 14)) << 32;   // stride between 8-row groups, version 1
   const uint32_t a_lo = ((abase >> 4) & 0x3FFFu) | ((uint32_t)((SB * 16) >> 4) << 16);
   const uint32_t b_lo = ((bbase >> 4) & 0x3FFFu) | ((uint32_t)((NSL * 16 * N) >> 4) << 16);
@@ -463,8 +469,8 @@ __device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, u
     for (int r0 = 0; r0 < ntot; r0 += 256) {
       const int np = (ntot - r0 < 256) ? ntot - r0 : 256;
       const uint64_t bd = HI | (uint64_t)(b_lo + (uint32_t)r0);   // r0 rows of 16 bytes
-      // A format (bits [7, 10)): 1 = signed 8 bit for the top slice, 0 = unsigned for the plain low bytes
-      umma_i8(tmem_base + (uint32_t)(i * N + r0), ad, bd, idesc_i8(SB, np) & ~((i == 0) ? 0u : (1u << 7)), (i == 0) ? first : 1u);
+      // A format (bits [7, 10)): 1 = signed 8 bit for the top slice of U, 0 = unsigned for W's top slice and the plain low bytes
+      umma_i8(tmem_base + (uint32_t)(i * N + r0), ad, bd, (idesc_i8(SB, np) & ~(1u << 7)) | ((i == 0) ? (top_signed << 7) : 0u), (i == 0) ? first : 1u);
     }
   }
 }
@@ -541,8 +547,8 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
         const bool last = ks == tl.nks - 1;
         if (elect_one()) {
           if (MODE != 1) {
-            if (tl.N == 64) k2s_issue_step<64>(abase, abase + A_STEP7, tmem_base, first);
-            else k2s_issue_step<32>(abase, abase + A_STEP7, tmem_base, first);
+            if (tl.N == 64) k2s_issue_step<64>(abase, abase + A_STEP7, tmem_base, first, tl.isu);
+            else k2s_issue_step<32>(abase, abase + A_STEP7, tmem_base, first, tl.isu);
           }
           umma_commit(&empty[st]);
           if (last) umma_commit(tfull);

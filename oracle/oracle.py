@@ -71,6 +71,8 @@ def load_c() -> C.CDLL:
         lib.oracle_voigt.argtypes = [_pd, C.c_long, C.c_double, C.c_double, C.c_int, _pd]
         lib.oracle_log_mvnpdf_low_rank.restype = C.c_double
         lib.oracle_log_mvnpdf_low_rank.argtypes = [_pd, _pd, _pd, _pd, C.c_long, C.c_int]
+        lib.oracle_log_mvnpdf_low_rank_ld.restype = C.c_double
+        lib.oracle_log_mvnpdf_low_rank_ld.argtypes = [_pd, _pd, _pd, _pd, C.c_long, C.c_int]
         lib.oracle_process_quasar.restype = C.c_long
         lib.oracle_process_quasar.argtypes = [C.c_long, C.c_long, _pd, C.POINTER(C.c_int), _pd, _pd, _pd, _pd, _pd,
                                               C.c_double, C.c_double, C.c_long, _pd, _pd, C.c_int, C.c_int,
@@ -161,6 +163,15 @@ def log_mvnpdf_low_rank_c(y, mu, M, d):
     Mf = np.ascontiguousarray(np.asfortranarray(M).ravel(order="F"))
     y, mu, d = (np.ascontiguousarray(a, dtype=np.float64) for a in (y, mu, d))
     return load_c().oracle_log_mvnpdf_low_rank(_p(y), _p(mu), _p(Mf), _p(d), n, k)
+
+
+def log_mvnpdf_low_rank_extended(y, mu, M, d):
+    """The same statements in x87 extended precision (oracle/lmlr_extended.c): how far the reference's fp64
+    evaluation is from the exact value of its own formula (tools/parity_truth.py)."""
+    n, k = M.shape
+    Mf = np.ascontiguousarray(np.asfortranarray(M).ravel(order="F"))
+    y, mu, d = (np.ascontiguousarray(a, dtype=np.float64) for a in (y, mu, d))
+    return load_c().oracle_log_mvnpdf_low_rank_ld(_p(y), _p(mu), _p(Mf), _p(d), n, k)
 
 
 def log_mvnpdf_dense(y, mu, M, d):
