@@ -249,6 +249,7 @@ static void launch_k2s(int mode, int stages, unsigned grid, cudaStream_t st, Arg
   else if (mode == 2 && stages == 3) sl::contract_slices_tiles_kernel<2, 3><<<grid, sl::K2S_THREADS, sl::k2s_smem(3), st>>>(args...);
   else if (mode == 1) sl::contract_slices_tiles_kernel<1, 5><<<grid, sl::K2S_THREADS, sl::k2s_smem(5), st>>>(args...);
   else if (mode == 2) sl::contract_slices_tiles_kernel<2, 5><<<grid, sl::K2S_THREADS, sl::k2s_smem(5), st>>>(args...);
+  else if (mode == 3) sl::contract_slices_tiles_kernel<3, 5><<<grid, sl::K2S_THREADS, sl::k2s_smem(5), st>>>(args...);
   else if (stages == 3) sl::contract_slices_tiles_kernel<0, 3><<<grid, sl::K2S_THREADS, sl::k2s_smem(3), st>>>(args...);
   else sl::contract_slices_tiles_kernel<0, 5><<<grid, sl::K2S_THREADS, sl::k2s_smem(5), st>>>(args...);
 }
@@ -709,6 +710,7 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<0, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(3)));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<1, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(5)));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<2, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(5)));
+  CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<3, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(5)));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<1, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(3)));
   CREATE_TRY(cudaFuncSetAttribute(dla::sl::contract_slices_tiles_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dla::sl::k2s_smem(3)));
   // the contraction of one chunk and the Voigt kernel of the next share SMs: both ask for the largest shared-memory

@@ -419,7 +419,7 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
 // K2s.  Persistent: CTA b walks the work items t = b, b + gridDim.x, ...; item t = ((ql * nsb) + sb) * 5 + unit, so the
 // five units of a sample block run at the same time on neighbouring SMs and share the block's planes through L2.
 // Warp 0: TMA producer (two 1-D bulk copies per K step), warp 1: MMA issue (28 kind::i8 MMAs per K step), warps
-// 2..5: epilogue (TMEM -> fp64 -> G).  MODE 1 / 2 (diagnosis): no MMA / no loads after the first ring fill.
+// 2..5: epilogue (TMEM -> fp64 -> G).  MODE 1 / 2 / 3 (diagnosis): no MMA / no loads after the first ring fill / no epilogue work.
 // ------------------------------------------------------------------------------------------------------------
 struct K2sTile {
   const int8_t* a;
@@ -456,6 +456,14 @@ __device__ __forceinline__ bool elect_one() {
   asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
   return pred != 0;
 }
+// a 2^16 + b 2^8 + c for three int32 accumulators: exact, below 2^48 in magnitude
+__device__ __forceinline__ long long combine3(int a, int b, int c) {
+  return (((long long)a << 8) + (long long)b << 8) + (long long)c;
+}
+// int64 (|x| < 2^51) -> double without the conversion unit: x + 2^51 placed in the mantissa of 2^52, minus the bias
+__device__ __forceinline__ double i64_to_f64(long long x) {
+  return __longlong_as_double((x + 0x0008000000000000ll) + 0x4330000000000000ll) - 6755399441055744.0;   // 2^52 + 2^51
+}
 template <int N>
 __device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, uint32_t tmem_base, uint32_t first, uint32_t top_signed) {
   constexpr uint64_t HI = (uint64_t)(((128u >> 4) & 0x3FFFu) | (1u << 14)) << 32;   // stride between 8-row groups, version 1
@@ -475,9 +483,9 @@ __device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, u
   }
 }
 
-// launch bounds: the second number only caps the registers (shared memory allows one CTA per SM anyway)
+// one CTA per SM (shared memory): up to 204 registers per thread, the epilogue warps use them for two buffers
 template <int MODE, int K2S_STAGES>
-__global__ void __launch_bounds__(K2S_THREADS, 2)
+__global__ void __launch_bounds__(K2S_THREADS, 1)
 contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq, int nsb, const SliceLayout L, const int8_t* __restrict__ Aw,
                              const int8_t* __restrict__ Au, const int8_t* __restrict__ Bt, const double* __restrict__ colscale,
                              double* __restrict__ G) {
@@ -569,27 +577,56 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
       tc_fence_after();
       double* grow = G + ((int64_t)tl.ql * S_pad + (int64_t)tl.sb * SB + row) * L.gcols + tl.col0;
       const double* cs = colscale + (int64_t)tl.ql * L.gcols + tl.col0;
-      const int nc8h = tl.N / 16;
-#pragma unroll 1
-      for (int c8 = half * nc8h; c8 < (half + 1) * nc8h; ++c8) {
-        uint32_t r[NSL][8];
+      const int nc8h = (MODE == 3) ? 0 : tl.N / 16;   // 4 or 2 groups of eight columns for this warp
+      const int cb = half * nc8h;
+      // two register buffers: the TMEM loads of group i + 1 are in flight while group i is recombined and stored, and
+      // the accumulators are handed back to the MMA warp as soon as the last group sits in registers
+      uint32_t r[2][NSL][8];
+      auto load = [&](int i, uint32_t (&dst)[NSL][8]) {
 #pragma unroll
-        for (int dgn = 0; dgn < NSL; ++dgn) tmem_ld8(tlane + (uint32_t)(dgn * tl.N + c8 * 8), r[dgn]);
-        tmem_ld_wait();
+        for (int dgn = 0; dgn < NSL; ++dgn) tmem_ld8(tlane + (uint32_t)(dgn * tl.N + (cb + i) * 8), dst[dgn]);
+      };
+      auto emit = [&](int i, const uint32_t (&src)[NSL][8]) {
+        const int c8 = cb + i;
         double out[8];
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
-          double v = i32_to_f64(r[NSL - 1][c]);
+#if defined(DLA_K2S_EPI_HORNER)   // tuning build: seven conversions and six fma per column
+          double v = i32_to_f64(src[NSL - 1][c]);
 #pragma unroll
-          for (int dgn = NSL - 2; dgn >= 0; --dgn) v = fma(v, 0.00390625, i32_to_f64(r[dgn][c]));
+          for (int dgn = NSL - 2; dgn >= 0; --dgn) v = fma(v, 0.00390625, i32_to_f64(src[dgn][c]));
           out[c] = v * __ldg(cs + c8 * 8 + c);
+#else
+          // three diagonals at a time, exactly, in 64-bit integers (|.| < 2^48), then two fp64 steps instead of six
+          const long long g0 = combine3((int)src[0][c], (int)src[1][c], (int)src[2][c]);
+          const long long g1 = combine3((int)src[3][c], (int)src[4][c], (int)src[5][c]);
+          double v = fma(i32_to_f64(src[6][c]), 0.00390625, i64_to_f64(g1));             // g1 + acc_6 2^-8
+          v = fma(v, 5.9604644775390625e-08, i64_to_f64(g0));                            // g0 + (...) 2^-24
+          out[c] = v * (__ldg(cs + c8 * 8 + c) * 1.52587890625e-05);                     // sum_d acc_d 2^(-8 d) = v 2^-16
+#endif
         }
 #pragma unroll
         for (int c = 0; c < 8; c += 2) *reinterpret_cast<double2*>(grow + c8 * 8 + c) = make_double2(out[c], out[c + 1]);
+      };
+      if (nc8h > 0) load(0, r[0]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (i < nc8h) {
+          tmem_ld_wait();
+          if (i + 1 < nc8h) load(i + 1, r[(i + 1) & 1]);
+          else {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) bar_arrive(tempty);
+          }
+          emit(i, r[i & 1]);
+        }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) bar_arrive(tempty);
+      if (nc8h == 0) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) bar_arrive(tempty);
+      }
     }
   }
   tc_fence_before();
