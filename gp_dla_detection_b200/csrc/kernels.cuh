@@ -265,6 +265,22 @@ __device__ __forceinline__ double lds_f64(uint32_t a) {
   asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
   return v;
 }
+// read-only tables / staged inputs: plain (non-volatile) loads the compiler may schedule freely
+__device__ __forceinline__ double lds_f64_ro(uint32_t a) {
+  double v;
+  asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ double2 lds_f64x2_ro(uint32_t a) {
+  double2 v;
+  asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+  return v;
+}
+// a table of doubles in shared memory by its 32-bit shared-window address (no generic-pointer arithmetic in the loop)
+struct SmemTab {
+  uint32_t base;
+  __device__ __forceinline__ double operator[](int i) const { return lds_f64_ro(base + 8u * (uint32_t)i); }
+};
 __device__ __forceinline__ void sts_f64(uint32_t a, double v) {
   asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
 }
@@ -525,7 +541,8 @@ constexpr int K1S_THREADS = TS;  // one CTA = 64 hypotheses x ONE spectrum segme
 
 // exp(t), t <= 0, result >= 2^-1020 (t is clamped at -707: a transmission of 1e-307 and one of 0
 // are the same number to every consumer: a^2 underflows either way).  NaN propagates.
-__device__ __forceinline__ double exp_tab256(double t, const double* __restrict__ etab_s) {
+template <class Tab>
+__device__ __forceinline__ double exp_tab256(double t, Tab etab_s) {
   // clamp on the high word alone (t <= 0 here, so a larger unsigned high word is a more negative t; the low
   // word stays: t lands in [-707.001, -707]); a positive NaN compares below the threshold and propagates
   t = __hiloint2double((int)min((unsigned)__double2hiint(t), 0xC0861800u), __double2loint(t));  // hi word of -707.0
@@ -575,10 +592,10 @@ __device__ __forceinline__ double wing_7(double sp, int j, double ncw, double to
 // The velocity is formed with ONE fma first; beyond 64 Doppler widths that differs from voigt.c:287's
 // separately rounded product by <= 2^-53 c / v <= 4e-14 relative.  Closer to a line the step is
 // redone with the reference's rounding (warp-uniform branch, rare).
-template <int NPIX>
+template <int NPIX, class Tab = const double*>
 __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const double (&mult)[3],
                                          const double (&ncw)[3], const double (&nc1)[3], const double (&nc2)[3],
-                                         double N, const double* etab_s, double (&out)[NPIX]) {
+                                         double N, Tab etab_s, double (&out)[NPIX]) {
   double sp[NPIX][3];
   int minhi = 0x7fffffff;
   const double negc = -g_lines.c_cgs;
@@ -640,10 +657,12 @@ __device__ __forceinline__ void raw_lane(const double (&lambda)[NPIX], const dou
 }
 
 // weights of the four kept pixels 4g..4g+3 from the 10-point window raw[4g .. 4g+9]
-template <bool TAIL>
+// STRIDE = double2's per pixel record: 2 = {omega2, noise}, {mu, flux}; 3 = the same + one more pair handed back in
+// extra[] (the slice kernel keeps its two reciprocal scales there, so a pixel is one address and three 16-byte loads)
+template <bool TAIL, int STRIDE = 2>
 __device__ __forceinline__ void weights_lane_core(const double (&win)[10], int g, int n, int jdead, const double2* px /* shared */,
                                                   double (&w)[4], double (&u)[4], double& q0acc, double& ldacc, double& dprod,
-                                                  int& esum) {
+                                                  int& esum, double2* extra = nullptr) {
   // d within 2^+-200 (integer compares on the high word): the product of four such factors and a value in
   // [1,2) cannot leave the normal range
   constexpr unsigned LO = (1023 - 200) << 20, SPAN = 400u << 20;
@@ -654,8 +673,9 @@ __device__ __forceinline__ void weights_lane_core(const double (&win)[10], int g
     const int j = 4 * g + h;
     const bool live = !TAIL || j < n;
     const int jc = live ? j : jdead;
-    const double2 p01 = px[2 * jc];      // {omega2, noise}
-    const double2 p23 = px[2 * jc + 1];  // {mu, flux}
+    const double2 p01 = px[STRIDE * jc];      // {omega2, noise}
+    const double2 p23 = px[STRIDE * jc + 1];  // {mu, flux}
+    if (STRIDE == 3) extra[h] = px[STRIDE * jc + 2];
     // voigt.c:297-299: zero-initialised, accumulated in tap order (0 + x y rounds like x y)
     double a = win[h] * dla_instrument_profile[0];
 #pragma unroll

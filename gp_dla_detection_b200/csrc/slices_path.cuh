@@ -260,13 +260,16 @@ __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const S
 //   planes: a_off + ((sb * nks + ks) * 7 + slice) * 4096 + (chunk & 1) * 2048 + row * 16
 // ------------------------------------------------------------------------------------------------------------
 // m[h] = fma(value, 1 / scale, MAGIC): bits(m) - bits(MAGIC) = X = round(t 2^52) (two's complement, |X| < 2^52);
-// slice i = byte 6 - i of X; out[i] = the four pixels' slice-i bytes.  Only the high word needs the subtraction.
-template <uint32_t MAGIC_HI>
+// slice i = byte 6 - i of 16 X; out[i] = the four pixels' slice-i bytes.
+// The exponent field of m never reaches a slice (the top slice is bits 16..23 of the shifted high word = mantissa bits
+// 44..51), so bits(MAGIC) need not be subtracted: for W (MAGIC = 1.0) the mantissa is X itself; for U (MAGIC = 1.5)
+// it is X + 2^51, i.e. the two's-complement X with its sign bit flipped -- one xor on the top-slice word (TOPFLIP).
+template <bool TOPFLIP>
 __device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NSL]) {
   uint32_t lo[4], hi[4];
 #pragma unroll
   for (int h = 0; h < 4; ++h) {
-    const uint32_t l = (uint32_t)__double2loint(m[h]), hh = (uint32_t)__double2hiint(m[h]) - MAGIC_HI;
+    const uint32_t l = (uint32_t)__double2loint(m[h]), hh = (uint32_t)__double2hiint(m[h]);
     lo[h] = l << 4;                         // 16 X: the top slice becomes bits 44..51 of X
     hi[h] = __funnelshift_l(l, hh, 4);
   }
@@ -280,7 +283,7 @@ __device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NS
   const uint32_t t6 = __byte_perm(hi[0], hi[1], 0x0062), t7 = __byte_perm(hi[2], hi[3], 0x0062);
   out[2] = __byte_perm(t4, t5, 0x5410);
   out[1] = __byte_perm(t4, t5, 0x7632);
-  out[0] = __byte_perm(t6, t7, 0x5410);
+  out[0] = __byte_perm(t6, t7, 0x5410) ^ (TOPFLIP ? 0x80808080u : 0u);
 }
 
 // MINB: resident CTAs per SM the kernel is compiled for (3 -> 168 registers, 4 -> 128).  PXS: the per-pixel records
@@ -312,17 +315,19 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
   const int nsteps = (g1 > g0) ? g1 - g0 + 2 : 0;
   double* lam_s = k1q_smem;
   double2* px_s = reinterpret_cast<double2*>(k1q_smem + lam_cap);
-  double2* sc_s = px_s + 2 * (PXS ? px_cap : 0);
-  uint32_t* stg_s = reinterpret_cast<uint32_t*>(sc_s + (PXS ? px_cap : 0)) + tid;   // [14 pieces][3 steps][128 lanes]
+  // PXS: 48-byte records {omega2, noise}, {mu, flux}, {1/c_w, 1/c_u} per pixel
+  uint32_t* stg_s = reinterpret_cast<uint32_t*>(px_s + 3 * (PXS ? px_cap : 0)) + tid;   // [14 pieces][3 steps][128 lanes]
   for (int i = tid; i < 256; i += K1Q_THREADS) etab_s[i] = etab256[i];
   {
     const double* lam_g = padded_wavelengths + d.pad_off;
     for (int i = tid; i < 4 * nsteps; i += K1Q_THREADS) lam_s[i] = __ldg(lam_g + min(max(4 * g0 - 2 + i, lbase), llast));
     if (PXS) {
       const double2* px_g = pix4 + 2 * (d.pix_off + j0);
-      for (int i = tid; i < 2 * (j1 - j0); i += K1Q_THREADS) px_s[i] = __ldg(px_g + i);
       const double2* sc_g = isc + d.pix_off + j0;
-      for (int i = tid; i < j1 - j0; i += K1Q_THREADS) sc_s[i] = __ldg(sc_g + i);
+      for (int i = tid; i < 3 * (j1 - j0); i += K1Q_THREADS) {
+        const int pxl = i / 3, part = i - 3 * pxl;
+        px_s[i] = (part < 2) ? __ldg(px_g + 2 * pxl + part) : __ldg(sc_g + pxl);
+      }
     }
   }
   __syncthreads();
@@ -340,8 +345,11 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
     nc1[j] = ncw[j] * g_lines.g1p[j];
     nc2[j] = ncw[j] * g_lines.gq[2];
   }
-  const double2* px = PXS ? px_s - 2 * j0 : pix4 + 2 * d.pix_off;   // indexed by 2 * kept pixel
-  const double2* sc = PXS ? sc_s - j0 : isc + d.pix_off;            // indexed by kept pixel
+  constexpr int PSTR = PXS ? 3 : 2;                                     // double2's per pixel record
+  const double2* px = PXS ? px_s - 3 * j0 : pix4 + 2 * d.pix_off;      // indexed by PSTR * kept pixel
+  const double2* sc = isc + d.pix_off;                                  // !PXS: the reciprocal scales, by kept pixel
+  const uint32_t lam_a = smem_u32(lam_s);                               // 32-bit shared-window addresses: no generic
+  const SmemTab etab{smem_u32(etab_s)};                                 // pointer arithmetic inside the step loop
   const int jdead = (j1 > j0) ? j0 : 0;  // a live pixel of this segment stands in for dead ones (values discarded)
   const int gfull = n >> 2;
   const int64_t S_pad = (int64_t)nsb * SB;
@@ -359,10 +367,10 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
   for (int st = 0; st < nsteps; ++st) {
     double l4[4], r4[4];
     {
-      const double2 la = reinterpret_cast<const double2*>(lam_s)[2 * st], lb = reinterpret_cast<const double2*>(lam_s)[2 * st + 1];
+      const double2 la = lds_f64x2_ro(lam_a + 32u * (uint32_t)st), lb = lds_f64x2_ro(lam_a + 32u * (uint32_t)st + 16u);
       l4[0] = la.x, l4[1] = la.y, l4[2] = lb.x, l4[3] = lb.y;
     }
-    raw_lane<4>(l4, mult, ncw, nc1, nc2, N, etab_s, r4);
+    raw_lane<4, SmemTab>(l4, mult, ncw, nc1, nc2, N, etab, r4);
 #pragma unroll
     for (int t = 0; t < 6; ++t) win[t] = win[t + 4];
 #pragma unroll
@@ -370,23 +378,32 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
     if (st >= 2) {
       const int g = g0 + st - 2;
       double w[4], u[4];
-      if (g < gfull) weights_lane_core<false>(win, g, n, jdead, px, w, u, q0acc, ldacc, dprod, esum);
-      else if (have_px) weights_lane_core<true>(win, g, n, jdead, px, w, u, q0acc, ldacc, dprod, esum);
-      else {
+      double2 is[4];
+      if (g < gfull) {
+        weights_lane_core<false, PSTR>(win, g, n, jdead, px, w, u, q0acc, ldacc, dprod, esum, is);
+        if (!PXS) {
 #pragma unroll
-        for (int h = 0; h < 4; ++h) w[h] = u[h] = 0.0;
+          for (int h = 0; h < 4; ++h) is[h] = sc[4 * g + h];
+        }
+      } else if (have_px) {
+        weights_lane_core<true, PSTR>(win, g, n, jdead, px, w, u, q0acc, ldacc, dprod, esum, is);   // w = u = 0 beyond n
+        if (!PXS) {
+#pragma unroll
+          for (int h = 0; h < 4; ++h) is[h] = sc[(4 * g + h < n) ? 4 * g + h : jdead];
+        }
+      } else {
+#pragma unroll
+        for (int h = 0; h < 4; ++h) w[h] = u[h] = 0.0, is[h] = make_double2(0.0, 0.0);
       }
       double mw[4], mu_[4];
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
-        const int j = 4 * g + h;
-        const double2 is = have_px ? sc[(j < n) ? j : jdead] : make_double2(0.0, 0.0);
-        mw[h] = fma(w[h], is.x, 1.0);
-        mu_[h] = fma(u[h], is.y, 1.5);
+        mw[h] = fma(w[h], is[h].x, 1.0);
+        mu_[h] = fma(u[h], is[h].y, 1.5);
       }
       uint32_t nw[NSL], nu[NSL];
-      digits4<0x3FF00000u>(mw, nw);
-      digits4<0x3FF80000u>(mu_, nu);
+      digits4<false>(mw, nw);
+      digits4<true>(mu_, nu);
       const int qs = g & 3;
       if (qs < 3) {
         uint32_t* slot = stg_s + qs * K1Q_THREADS;

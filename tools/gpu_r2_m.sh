@@ -1,0 +1,12 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_slices.py -m gpu -x -q > gpurun_out/m2_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/m2_pytest.log
+timeout 600 python tools/slices_diag.py --quasars 192 --oracle 2 --reps 3 --variants DLA_B200_K1Q=1 DLA_B200_K1Q=2 > gpurun_out/m2_diag.log 2>&1; echo "diag rc=$?"
+python - <<'PY'
+import json
+for l in open('gpurun_out/m2_diag.log'):
+    if l.startswith('{'):
+        d=json.loads(l)
+        if 'timing' in d: print(d['path'], d.get('bitwise_equal_to_default'), {k: round(v,3) for k,v in d['timing'].items() if k in ('ms_total','ms_voigt','ms_contract','ms_chol')})
+        else: print(d)
+PY
