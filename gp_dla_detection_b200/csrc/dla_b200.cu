@@ -153,7 +153,7 @@ struct dla_ctx {
   bool use_fused = false;            // DLA_B200_FUSED=1: fused_voigt_contract_kernel (W/U never leave the SM)
   bool use_slices = true;            // DLA_B200_CONTRACT=dmma turns the int8 tcgen05 contraction off (FP64 DMMA kernels)
   int k2s_mode = 0;                  // DLA_B200_K2S_MODE=1/2: diagnosis builds of the contraction (no MMA / no loads)
-  int k1q_variant = 0;               // DLA_B200_K1Q=0/1/2: Voigt kernel build when it runs alone (launch_chunk_slices)
+  int k1q_variant = 1;               // DLA_B200_K1Q=0/1/2: Voigt kernel build when it runs alone (launch_chunk_slices)
   int k2s_stages = 5;                // DLA_B200_K2S_STAGES=3/5: ring depth of the contraction when it runs alone
   int overlap_chunks = 16;           // DLA_B200_OVERLAP_CHUNKS: chunks an overlapped batch is split into (at most)
   bool overlap = false;               // DLA_B200_OVERLAP=0: contraction of chunk i NOT run under the Voigt kernel of chunk i + 1
@@ -295,8 +295,8 @@ static int launch_chunk_slices(dla_ctx* c, const Inputs& in, const Chunk& ch, in
     NvtxRange r("dla K1s voigt -> int8 planes");
     const int cmax = (nch + nseg - 1) / nseg;   // 16-pixel chunks per segment
     const int lam_cap = 16 * cmax + 8, px_cap = 16 * cmax;
-    const int variant = ov ? 2 : c->k1q_variant;   // 0: 168 registers, records in shared memory; 1: 128 registers, same; 2: 128, records from L1
-    const size_t smem = (size_t)lam_cap * 8 + (variant == 2 ? 0 : (size_t)px_cap * 48) + (size_t)2 * sl::NSL * 3 * sl::K1Q_THREADS * 4;
+    const int variant = ov ? 2 : c->k1q_variant;   // 0: 3 CTAs per SM (162 registers), records in shared memory; 1 (default): 4 CTAs (126 registers, no spills), same; 2: 4 CTAs, records from L1
+    const size_t smem = (size_t)lam_cap * 8 + (variant == 2 ? 0 : (size_t)px_cap * 48) + (size_t)4 * 3 * sl::K1Q_THREADS * 16;
     if (smem > 100 * 1024) BAD_ARG(c, "a quasar has too many pixels for the Voigt kernel's shared-memory staging");
     const unsigned grid = (unsigned)((int64_t)ch.nq * nsb * nseg);
 #define K1Q_ARGS in.desc, in.sq, ch.q0, nsb, S, d_offset, d_nhi, in.padded, in.pix4, c->d_isc.as<double2>(), \

@@ -256,7 +256,7 @@ __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const S
 // segment of the spectrum; segments are whole 16-pixel chunks.  Every step yields four pixels, i.e. one 32-bit
 // word of each of the 14 sixteen-byte pieces (7 slices of W, 7 of U) the lane owns; the pieces are complete after
 // four steps and leave as 16-byte stores, 512 contiguous bytes per warp and piece.  The words of the first three
-// steps wait in a per-lane shared-memory slot ([piece][step][lane]: conflict-free both ways), not in registers.
+// steps wait in a per-lane shared-memory slot ([slice quad][step][lane] x 16 B), not in registers.
 //   planes: a_off + ((sb * nks + ks) * 7 + slice) * 4096 + (chunk & 1) * 2048 + row * 16
 // ------------------------------------------------------------------------------------------------------------
 // m[h] = fma(value, 1 / scale, MAGIC): bits(m) - bits(MAGIC) = X = round(t 2^52) (two's complement, |X| < 2^52);
@@ -286,7 +286,7 @@ __device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NS
   out[0] = __byte_perm(t6, t7, 0x5410) ^ (TOPFLIP ? 0x80808080u : 0u);
 }
 
-// MINB: resident CTAs per SM the kernel is compiled for (3 -> 168 registers, 4 -> 128).  PXS: the per-pixel records
+// MINB: resident CTAs per SM the kernel is compiled for (3 -> 162 registers; 4 -> 126, the default, no spills).  PXS: the per-pixel records
 // {omega2, noise, mu, flux, 1/c_w, 1/c_u} of the segment are staged in shared memory (px_cap pixels, 48 B each);
 // otherwise they are warp-uniform global loads (L1 hits) and a CTA needs 26 KB only.
 template <int MINB, bool PXS>
@@ -316,7 +316,7 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
   double* lam_s = k1q_smem;
   double2* px_s = reinterpret_cast<double2*>(k1q_smem + lam_cap);
   // PXS: 48-byte records {omega2, noise}, {mu, flux}, {1/c_w, 1/c_u} per pixel
-  uint32_t* stg_s = reinterpret_cast<uint32_t*>(px_s + 3 * (PXS ? px_cap : 0)) + tid;   // [14 pieces][3 steps][128 lanes]
+  uint4* stg_s = reinterpret_cast<uint4*>(px_s + 3 * (PXS ? px_cap : 0)) + tid;   // [4 slice quads][3 steps][128 lanes] x 16 B
   for (int i = tid; i < 256; i += K1Q_THREADS) etab_s[i] = etab256[i];
   {
     const double* lam_g = padded_wavelengths + d.pad_off;
@@ -406,21 +406,24 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
       digits4<true>(mu_, nu);
       const int qs = g & 3;
       if (qs < 3) {
-        uint32_t* slot = stg_s + qs * K1Q_THREADS;
-#pragma unroll
-        for (int i = 0; i < NSL; ++i) {
-          slot[i * 3 * K1Q_THREADS] = nw[i];
-          slot[(NSL + i) * 3 * K1Q_THREADS] = nu[i];
-        }
+        // slice quads {W0..W3}, {W4..W6, -}, {U0..U3}, {U4..U6, -}: four 16-byte stores per step instead of fourteen words
+        uint4* slot = stg_s + qs * K1Q_THREADS;
+        slot[0] = make_uint4(nw[0], nw[1], nw[2], nw[3]);
+        slot[3 * K1Q_THREADS] = make_uint4(nw[4], nw[5], nw[6], 0u);
+        slot[6 * K1Q_THREADS] = make_uint4(nu[0], nu[1], nu[2], nu[3]);
+        slot[9 * K1Q_THREADS] = make_uint4(nu[4], nu[5], nu[6], 0u);
       } else {
         const int ch = g >> 2;
         const int64_t o = (int64_t)(ch >> 1) * A_STEP7 + (ch & 1) * (SB * 16);
 #pragma unroll
-        for (int i = 0; i < NSL; ++i) {
-          const uint32_t* a = stg_s + i * 3 * K1Q_THREADS;
-          const uint32_t* b = stg_s + (NSL + i) * 3 * K1Q_THREADS;
-          *reinterpret_cast<uint4*>(wq + o + i * (2 * SB * 16)) = make_uint4(a[0], a[K1Q_THREADS], a[2 * K1Q_THREADS], nw[i]);
-          *reinterpret_cast<uint4*>(uq + o + i * (2 * SB * 16)) = make_uint4(b[0], b[K1Q_THREADS], b[2 * K1Q_THREADS], nu[i]);
+        for (int q = 0; q < 4; ++q) {
+          const uint4 s0 = stg_s[(3 * q) * K1Q_THREADS], s1 = stg_s[(3 * q + 1) * K1Q_THREADS], s2 = stg_s[(3 * q + 2) * K1Q_THREADS];
+          int8_t* dst = ((q < 2) ? wq : uq) + o + (q & 1) * 4 * (2 * SB * 16);
+          const uint32_t* last = ((q < 2) ? nw : nu) + (q & 1) * 4;
+          *reinterpret_cast<uint4*>(dst) = make_uint4(s0.x, s1.x, s2.x, last[0]);
+          *reinterpret_cast<uint4*>(dst + (2 * SB * 16)) = make_uint4(s0.y, s1.y, s2.y, last[1]);
+          *reinterpret_cast<uint4*>(dst + 2 * (2 * SB * 16)) = make_uint4(s0.z, s1.z, s2.z, last[2]);
+          if ((q & 1) == 0) *reinterpret_cast<uint4*>(dst + 3 * (2 * SB * 16)) = make_uint4(s0.w, s1.w, s2.w, last[3]);
         }
       }
     }
