@@ -29,10 +29,25 @@ __device__ __forceinline__ void umma_f8(uint32_t tmem_d, uint64_t adesc, uint64_
       : "memory");
 }
 
+// A operand from tensor memory: one 128 x 256 bit copy (128 rows x 32 bytes = one slice of a K step) from shared memory,
+// then MMAs that name the TMEM address instead of a shared-memory descriptor
+__device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint64_t sdesc) {
+  asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(taddr), "l"(sdesc) : "memory");
+}
+__device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // A group of MMAs, all operands compile-time offsets from one warp-uniform base (the product kernel's form: the
 // descriptors live in uniform registers and the issue loop is UTCIMMA after UTCIMMA).
 //   PAT 0: 8 x (128 x N x 32), distinct accumulators     PAT 1: the slice K step of an N-column unit (10 or 7 wide MMAs)
 //   PAT 2: the slice K step as 28 separate 128 x N x 32 MMAs
+//   PAT 3: PAT 1 with the sample slices copied to tensor memory first (tcgen05.cp) and read from there by the MMAs
+//   PAT 4: PAT 3 without the copies (the A operand already in tensor memory): the MMAs alone
 template <int PAT, int N, int KIND, int LAYOUT>
 __device__ __forceinline__ void issue_group(uint32_t base, uint32_t tmem_base) {
   constexpr uint32_t SBO = LAYOUT == 0 ? 128u : 1024u;
@@ -57,6 +72,19 @@ __device__ __forceinline__ void issue_group(uint32_t base, uint32_t tmem_base) {
       for (int r0 = 0; r0 < ntot; r0 += 256) {
         const int np = ntot - r0 < 256 ? ntot - r0 : 256;
         mma((uint32_t)(i * N + r0), (uint32_t)i * (LAYOUT == 0 ? 4096u : 16384u), (uint32_t)r0 * (LAYOUT == 0 ? 16u : 128u), np);
+      }
+    }
+  } else if (PAT == 3 || PAT == 4) {
+    constexpr uint32_t ACOL = 448;   // accumulators [0, 7 N), sample slices [448, 504): 8 columns of 32 bits per slice
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+      if (PAT == 3) tmem_cp_128x256b(tmem_base + ACOL + 8u * i, HI | (uint64_t)(a_lo + ((uint32_t)i * 4096u >> 4)));
+      const int ntot = (7 - i) * N;
+#pragma unroll
+      for (int r0 = 0; r0 < ntot; r0 += 256) {
+        const int np = ntot - r0 < 256 ? ntot - r0 : 256;
+        umma_i8_ts(tmem_base + (uint32_t)(i * N + r0), tmem_base + ACOL + 8u * i,
+                   HI | (uint64_t)(b_lo + (((uint32_t)r0 * 16u) >> 4)), idesc_i8(128, np), 1u);
       }
     }
   } else {
@@ -151,5 +179,9 @@ int main() {
   run<2, 64, 0, 0>("slice K step, 64-column unit, 28 separate MMAs", 28, 896);
   run<2, 32, 0, 0>("slice K step, 32-column unit, 28 separate MMAs", 28, 448);
   run<1, 64, 1, 0>("slice K step, 64-column unit, wide MMAs", 10, 896);
+  run<3, 64, 0, 0>("slice K step, 64-column unit, wide MMAs, A copied to TMEM per slice", 10, 896);
+  run<4, 64, 0, 0>("slice K step, 64-column unit, wide MMAs, A resident in TMEM", 10, 896);
+  run<3, 32, 0, 0>("slice K step, 32-column unit, wide MMAs, A copied to TMEM per slice", 7, 448);
+  run<4, 32, 0, 0>("slice K step, 32-column unit, wide MMAs, A resident in TMEM", 7, 448);
   return 0;
 }
