@@ -1858,7 +1858,7 @@ contract_block_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb, cons
   }
 }
 
-// One warp per sample: bordered matrix [[I + G, v], [v^T, q0]] in shared memory (row stride k + 2),
+// One warp per sample: bordered matrix [[I + G, v], [v^T, q0]] in shared memory (odd row stride >= k + 2),
 // right-looking Cholesky over the first k columns; the corner ends as q0 - t^T t and the product of
 // the pivots (kept in [1,2) with an integer exponent) gives log|B| (log_mvnpdf_low_rank.m:23-32).
 constexpr int CHG_WARPS = 4;

@@ -659,12 +659,18 @@ contract_slices_tiles_kernel(const SliceQuasar* __restrict__ sq, int q0, int nq,
 
 // ------------------------------------------------------------------------------------------------------------
 // K2c.  log_mvnpdf_low_rank.m:23-32 from the rows of G: one quad of lanes per sample (chol_logp_quad, kernels.cuh),
-// 32 samples per CTA, their rows (2 KB each) brought in by 32 bulk copies into padded shared-memory rows.
+// K2C_ROWS samples per CTA, their rows (2 KB each) brought in by as many bulk copies into padded shared-memory rows.
 // ------------------------------------------------------------------------------------------------------------
-constexpr int K2C_ROWS = 32;
+#ifndef DLA_K2C_ROWS
+#define DLA_K2C_ROWS 16
+#endif
+#ifndef DLA_K2C_MINB
+#define DLA_K2C_MINB 5
+#endif
+constexpr int K2C_ROWS = DLA_K2C_ROWS;   // samples per CTA: 64 threads, five CTAs = 10 warps per SM at 192 registers (32 rows, 2 CTAs: 8 warps, +18 % time)
 constexpr int K2C_LD = GCOLS + 2;   // padded row (doubles): the eight samples of a warp start in different banks
 constexpr size_t K2C_SMEM = (size_t)K2C_ROWS * K2C_LD * 8 + 16;
-__global__ void __launch_bounds__(K2C_ROWS * 4, 2)
+__global__ void __launch_bounds__(K2C_ROWS * 4, DLA_K2C_MINB)
 chol_rows_kernel(const QuasarDesc* __restrict__ desc, int q0, int nsb /* 128-sample blocks */, int64_t S,
                  const double* __restrict__ G, const double* __restrict__ aux, const int32_t* __restrict__ perm,
                  double* __restrict__ sample_ll /* [nq][S], caller order */, double* __restrict__ ll_no, int k, int nseg) {
