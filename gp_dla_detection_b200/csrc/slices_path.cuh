@@ -437,9 +437,9 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
 
 // ------------------------------------------------------------------------------------------------------------
 // K2s.  Persistent: CTA b walks the work items t = b, b + gridDim.x, ...; item t = ((ql * nsb) + sb) * 5 + unit, so the
-// five units of a sample block run at the same time on neighbouring SMs and share the block's planes through L2.
-// Warp 0: TMA producer (two 1-D bulk copies per K step), warp 1: MMA issue (28 kind::i8 MMAs per K step), warps
-// 2..5: epilogue (TMEM -> fp64 -> G).  MODE 1 / 2 / 3 (diagnosis): no MMA / no loads after the first ring fill / no epilogue work.
+// units of a sample block (five at k <= 20) run at the same time on neighbouring SMs and share the block's planes
+// through L2.  Warp 0: TMA producer (two 1-D bulk copies per K step), warp 1: MMA issue (10 or 7 wide kind::i8 MMAs per
+// K step), warps 2..9: epilogue (TMEM -> two register buffers -> fp64 -> G).  MODE 1 / 2 / 3 (diagnosis): no MMA / no loads after the first ring fill / no epilogue work.
 // ------------------------------------------------------------------------------------------------------------
 struct K2sTile {
   const int8_t* a;

@@ -163,3 +163,34 @@ def test_K7_unit_profile_sample_equals_no_dla(oracle):
     nhi = samples.nhi_samples.copy(); nhi[2] = 0.0
     r = oracle.process_quasar_c(prepared[0], samples.offset_samples, nhi, -1.0, -1.0)
     assert r["sample_log_likelihoods_dla"][2] == r["log_likelihoods_no_dla"]
+
+
+def test_extended_precision_restatement_is_pinned_by_mpmath():
+    """oracle/lmlr_extended.c (log_mvnpdf_low_rank.m in x87 extended precision: the yardstick of tools/parity_truth.py)
+    against a 50-digit dense evaluation of log N(y; mu, M M' + diag d): it must be at least two orders of magnitude
+    closer to the exact value than the fp64 restatement's own rounding noise."""
+    mp = pytest.importorskip("mpmath")
+    from oracle import oracle as O
+    mp.mp.dps = 50
+    rng = np.random.default_rng(21)
+    worst_ext, worst_f64 = 0.0, 0.0
+    for n, k in ((24, 3), (60, 7), (120, 12)):
+        y = rng.normal(size=n)
+        mu = 0.1 * rng.normal(size=n)
+        M = 0.5 * rng.normal(size=(n, k))
+        d = rng.uniform(1e-3, 0.5, n)                      # low noise: the regime where q0 - t't cancels (SURVEY H3)
+        K = mp.matrix(n, n)
+        for i in range(n):
+            for j in range(n):
+                K[i, j] = mp.fsum(mp.mpf(float(M[i, a])) * mp.mpf(float(M[j, a])) for a in range(k))
+            K[i, i] += mp.mpf(float(d[i]))
+        r = mp.matrix([mp.mpf(float(y[i])) - mp.mpf(float(mu[i])) for i in range(n)])
+        quad = (r.T * mp.lu_solve(K, r))[0]
+        exact = -(quad + mp.log(mp.det(K)) + n * mp.log(2 * mp.pi)) / 2
+        ext = O.log_mvnpdf_low_rank_extended(y, mu, M, d)
+        f64 = O.log_mvnpdf_low_rank_c(y, mu, M, d)
+        worst_ext = max(worst_ext, abs(float(mp.mpf(ext) - exact) / float(exact)))
+        worst_f64 = max(worst_f64, abs(float(mp.mpf(f64) - exact) / float(exact)))
+    print(f"extended vs 50-digit exact: {worst_ext:.2e} relative; fp64 restatement: {worst_f64:.2e}")
+    assert worst_ext <= 4e-16          # the final rounding to double
+    assert worst_f64 <= 1e-11
