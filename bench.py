@@ -436,7 +436,9 @@ def run_ours(args):
         ach8 = int8_ops / t_contract / 1e12
         roofline = {"kernel": "contract_slices_tiles_kernel (K2s: exact-slice int8 tcgen05 contraction, 7 x 7 slices, "
                               "int32 TMEM accumulators, fp64 recombination)",
-                    "bound": "tensor", "achieved": ach8, "peak": int8_peak, "unit": "TOP/s (int8)", "frac": ach8 / int8_peak,
+                    "bound": "tensor", "achieved": ach8, "peak": int8_peak, "unit": "TFLOP/s", "frac": ach8 / int8_peak,
+                    "unit_note": "tensor-core operations per second on 8-bit integer operands (one multiply-add = 2), i.e. int8 TOP/s; "
+                                 "the fp64-equivalent flop rate is in fp64_equivalent",
                     "peak_nominal": INT8_NOMINAL_TOPS, "frac_of_nominal": ach8 / INT8_NOMINAL_TOPS,
                     "peak_sustained": int8_sustained, "frac_of_sustained": ach8 / int8_sustained, "g_columns": gcols,
                     "shape_bound": "the 7 x 7 slice scheme issues MMAs of 32..256 columns; measured cost max(N/2, 64 + N/6) clocks each "
