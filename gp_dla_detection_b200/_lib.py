@@ -15,11 +15,13 @@ DLA_OK = 0
 STATUS_NAMES = {0: "DLA_OK", -1: "DLA_ERR_BAD_ARG", -2: "DLA_ERR_CUDA", -3: "DLA_ERR_NO_DEVICE",
                 -4: "DLA_ERR_OOM", -5: "DLA_ERR_STATE"}
 
+NOALLOC_MAX_POINTS = 16384   # DLA_NOALLOC_MAX_POINTS of include/dla_b200.h
+
 # every symbol include/dla_b200.h declares
 EXPORTED_SYMBOLS = (
     "dla_abi_version", "dla_device_count", "dla_create", "dla_destroy", "dla_last_error",
     "dla_set_samples", "dla_eval_batch", "dla_stage_batch", "dla_run_staged", "dla_fetch_staged",
-    "dla_get_timing", "dla_voigt", "dla_log_mvnpdf_low_rank", "dla_set_model", "dla_eval_spectra",
+    "dla_get_timing", "dla_voigt", "dla_voigt_noalloc", "dla_log_mvnpdf_low_rank", "dla_set_model", "dla_eval_spectra",
     "dla_train_set_data", "dla_train_objective",
 )
 
@@ -114,6 +116,8 @@ def _load_locked() -> C.CDLL:
     lib.dla_get_timing.argtypes = [_ctx, C.POINTER(dla_timing)]
     lib.dla_voigt.restype = C.c_int
     lib.dla_voigt.argtypes = [_ctx, _pd, C.c_int64, C.c_double, C.c_double, C.c_int32, _pd]
+    lib.dla_voigt_noalloc.restype = C.c_int
+    lib.dla_voigt_noalloc.argtypes = [_ctx, _pd, C.c_int64, C.c_double, C.c_double, C.c_int32, _pd]
     lib.dla_log_mvnpdf_low_rank.restype = C.c_int
     lib.dla_log_mvnpdf_low_rank.argtypes = [_ctx, _pd, _pd, _pd, _pd, C.c_int64, C.c_int32, _pd]
     lib.dla_set_model.restype = C.c_int

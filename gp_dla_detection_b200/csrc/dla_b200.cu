@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <exception>
+#include <mutex>
 #include <new>
 #include <string>
 #include <thread>
@@ -146,6 +147,7 @@ struct dla_ctx {
   DevBuf d_offset, d_nhi, d_perm, d_etab256;
   bool have_samples = false;
   DevBuf seam[11];  // dla_voigt / dla_log_mvnpdf_low_rank: grow-only device arrays (no cudaMalloc per call)
+  double* noalloc_scratch = nullptr;  // device address of g_noalloc_scratch on this context's GPU (dla_voigt_noalloc)
   std::vector<double> h_set_offset, h_set_nhi, h_set_model;  // what the device holds now, as the caller passed it
   bool force_pixel_lane_k1 = false;  // DLA_B200_K1=pixel: always use voigt_weights_kernel
   bool force_tile_k2 = false;        // DLA_B200_K2=tile: one CTA per tile (contract_chol_kernel)
@@ -530,6 +532,29 @@ static int ensure_workspace(dla_ctx* c, int k, int64_t wu_doubles, int64_t bmat_
 // ------------------------------------------------------------------------------------------
 // ABI
 // ------------------------------------------------------------------------------------------
+// ------------------------------------------------------------------------------------------
+// dla_voigt_noalloc: scratch that is never allocated.  One file-scope device array per GPU that loads the library
+// (384 KB, held until the process exits): [0, MAX) staged wavelengths, [MAX, 2 MAX) raw transmissions (the kernel's
+// scratch, voigt.c:282-292), [2 MAX, 3 MAX) the broadened profile.  In host code the array's NAME is only a stand-in;
+// its device address comes from cudaGetSymbolAddress, once per device, with that device current (dla_create).
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_noalloc_scratch[3 * DLA_NOALLOC_MAX_POINTS];
+static std::mutex g_noalloc_mu;
+static double* g_noalloc_addr[64] = {};
+// `device` must be the current device
+static cudaError_t noalloc_scratch_address(int device, double** out) {
+  if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_addr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    g_noalloc_addr[device] = static_cast<double*>(p);
+  }
+  *out = g_noalloc_addr[device];
+  return cudaSuccess;
+}
+
 extern "C" {
 
 int dla_abi_version(void) { return DLA_B200_ABI_VERSION; }
@@ -595,6 +620,7 @@ int dla_create(dla_ctx** out, int device, const dla_params* p) {
     }                                                                                      \
   } while (0)
   CREATE_TRY(cudaSetDevice(device));
+  CREATE_TRY(noalloc_scratch_address(device, &c->noalloc_scratch));
   CREATE_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CREATE_TRY(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
   CREATE_TRY(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
@@ -1589,6 +1615,44 @@ static int dla_voigt_impl(dla_ctx* c, const double* lambdas, int64_t num_points,
   return rc;
 }
 
+// dla_voigt without any allocation: the same kernel on the file-scope scratch.  cudaMemcpyDefault: `lambdas` and
+// `profile` may be host or device pointers.
+static int dla_voigt_noalloc_impl(dla_ctx* c, const double* lambdas, int64_t num_points, double z, double N, int32_t num_lines,
+                                  double* profile) {
+  if (!c) return DLA_ERR_BAD_ARG;
+  if (!lambdas || !profile) BAD_ARG(c, "dla_voigt_noalloc: NULL pointer");
+  if (num_points < 7) BAD_ARG(c, "dla_voigt_noalloc: need at least 7 points (voigt.c:271)");
+  if (num_points > DLA_NOALLOC_MAX_POINTS)
+    BAD_ARG(c, "dla_voigt_noalloc: num_points exceeds DLA_NOALLOC_MAX_POINTS (16384), the size of the library's static "
+               "scratch; use dla_voigt for longer grids");
+  if (!c->noalloc_scratch) {
+    c->err = "dla_voigt_noalloc: the static scratch has no device address on this context";
+    return DLA_ERR_STATE;
+  }
+  if (num_lines <= 0 || num_lines > DLA_MAX_LINES) num_lines = DLA_MAX_LINES;  // voigt.c:266
+  CU_TRY(c, cudaSetDevice(c->device));
+  double* lam = c->noalloc_scratch;
+  double* raw = lam + DLA_NOALLOC_MAX_POINTS;
+  double* prof = raw + DLA_NOALLOC_MAX_POINTS;
+  // nothing has to start at zero: the kernel writes raw[0, num_points) and prof[0, num_points - 6) before it reads them;
+  // what an earlier call left beyond that is never touched
+  int rc = DLA_OK;
+  auto fail = [&](cudaError_t e, const char* what) {
+    c->err = std::string("dla_voigt_noalloc: ") + what + ": " + cudaGetErrorString(e);
+    rc = DLA_ERR_CUDA;
+  };
+  cudaError_t e;
+  if ((e = cudaMemcpyAsync(lam, lambdas, (size_t)num_points * 8, cudaMemcpyDefault, c->stream)) != cudaSuccess) fail(e, "copy in");
+  if (rc == DLA_OK) {
+    dla::voigt_single_kernel<<<1, 1024, 0, c->stream>>>(lam, (int)num_points, z, N, num_lines, raw, prof);
+    if ((e = cudaGetLastError()) != cudaSuccess) fail(e, "launch");
+  }
+  if (rc == DLA_OK && (e = cudaMemcpyAsync(profile, prof, (size_t)(num_points - 6) * 8, cudaMemcpyDefault, c->stream)) != cudaSuccess)
+    fail(e, "copy out");
+  if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess && rc == DLA_OK) fail(e, "sync");
+  return rc;
+}
+
 static int dla_log_mvnpdf_low_rank_impl(dla_ctx* c, const double* y, const double* mu, const double* M, const double* d,
                             int64_t n, int32_t k, double* log_p) {
   if (!c) return DLA_ERR_BAD_ARG;
@@ -1727,6 +1791,10 @@ int dla_train_objective(dla_ctx* c, const double* x, int32_t apply_priors, doubl
 
 int dla_voigt(dla_ctx* c, const double* lambdas, int64_t num_points, double z, double N, int32_t num_lines, double* profile) {
   return guarded(c, [&] { return dla_voigt_impl(c, lambdas, num_points, z, N, num_lines, profile); });
+}
+
+int dla_voigt_noalloc(dla_ctx* c, const double* lambdas, int64_t num_points, double z, double N, int32_t num_lines, double* profile) {
+  return guarded(c, [&] { return dla_voigt_noalloc_impl(c, lambdas, num_points, z, N, num_lines, profile); });
 }
 
 int dla_log_mvnpdf_low_rank(dla_ctx* c, const double* y, const double* mu, const double* M, const double* d, int64_t n, int32_t k, double* log_p) {

@@ -358,6 +358,16 @@ class DlaContext:
                                         _lib.ptr(out, C.c_double)))
         return out
 
+    def voigt_noalloc(self, lambdas, z, N, num_lines=None):
+        """dla_voigt_noalloc: voigt() on the library's static device scratch, no allocation in the call; at most
+        _lib.NOALLOC_MAX_POINTS wavelengths (no counterpart in the reference; see include/dla_b200.h)."""
+        lam = np.ascontiguousarray(lambdas, dtype=np.float64).ravel()
+        out = np.empty(max(lam.shape[0] - 6, 0), dtype=np.float64)
+        nl = 31 if num_lines is None else int(num_lines)
+        self._check(self._lib.dla_voigt_noalloc(self._ctx, _lib.ptr(lam, C.c_double), lam.shape[0], float(z), float(N), nl,
+                                                _lib.ptr(out, C.c_double)))
+        return out
+
     def log_mvnpdf_low_rank(self, y, mu, M, d):
         """log_p = log_mvnpdf_low_rank(y, mu, M, d) (log_mvnpdf_low_rank.m:5)."""
         y = np.ascontiguousarray(y, dtype=np.float64).ravel()

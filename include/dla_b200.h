@@ -192,6 +192,19 @@ int dla_get_timing(const dla_ctx *ctx, dla_timing *out);
  *   profile = voigt(lambdas, z, N, num_lines); profile has num_points-6 entries. */
 int dla_voigt(dla_ctx *ctx, const double *lambdas, int64_t num_points, double z, double N,
               int32_t num_lines, double *profile);
+/* dla_voigt_noalloc: NO COUNTERPART IN THE REFERENCE; added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, kernel and result as dla_voigt, but the call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine): the staged wavelengths, the kernel's scratch (the raw transmissions of voigt.c:282-292) and the
+ * profile live in ONE file-scope `static __device__` array of the library, 3 x DLA_NOALLOC_MAX_POINTS doubles =
+ * 384 KB, which every GPU that loads the library holds until the process exits; its device address is looked up
+ * once per device in dla_create.  `lambdas` and `profile` may be host or device pointers (cudaMemcpyDefault).
+ * num_points > DLA_NOALLOC_MAX_POINTS is rejected with DLA_ERR_BAD_ARG.  Every call on a device shares the array,
+ * which keeps the last call's contents (nothing in it has to start at zero: the kernel writes what it reads); calls
+ * that overlap on the GPU -- two contexts of one device used from two threads -- RACE on it. */
+#define DLA_NOALLOC_MAX_POINTS 16384
+int dla_voigt_noalloc(dla_ctx *ctx, const double *lambdas, int64_t num_points, double z, double N,
+                      int32_t num_lines, double *profile);
 /* dla_log_mvnpdf_low_rank = log_mvnpdf_low_rank.m:5-34:
  *   log N(y; mu, M M' + diag(d)); M column-major n x k, k <= 20. */
 int dla_log_mvnpdf_low_rank(dla_ctx *ctx, const double *y, const double *mu, const double *M,
