@@ -194,3 +194,23 @@ def test_any_rank_on_the_slice_path(oracle, k):
     assert got["_timing"]["contraction"] == 1
     ref = oracle_batch(oracle, mine, samples, sp.log_priors_dla, sp.log_priors_no_dla)
     assert_parity(got, ref)
+
+
+def test_spectra_longer_than_the_int32_accumulator_bound_take_the_fp64_kernels(oracle):
+    """The int32 slice accumulators are exact up to 9 362 pixels; the planner sends quasars of more than 8 192 kept pixels
+    to the FP64 kernels (here: the model on a 0.03 A grid, 10 134 pixels, twice the pipeline's finest)."""
+    from gp_dla_detection_b200 import synthetic
+    from gp_dla_detection_b200.process_qsos import prepare_quasar
+    from gp_dla_detection_b200.set_parameters import Parameters
+    S, k = 100, 20
+    params = Parameters(k=k, dlambda=0.03, num_dla_samples=S)
+    model = synthetic.make_model(k, 0.03, 20260077, params)
+    samples = synthetic.make_samples(S, params)
+    sp = synthetic.make_spectra(2, model, 20260078, False, params)
+    prepared = [prepare_quasar(w, f, v, m, z, model, params)
+                for w, f, v, m, z in zip(sp.all_wavelengths, sp.all_flux, sp.all_noise_variance, sp.all_pixel_mask, sp.z_qsos)]
+    assert min(p.n for p in prepared) > 8192
+    got = _run(prepared, samples, k, S, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert got["_timing"]["contraction"] == 0
+    ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
+    assert_parity(got, ref)
