@@ -214,3 +214,26 @@ def test_spectra_longer_than_the_int32_accumulator_bound_take_the_fp64_kernels(o
     assert got["_timing"]["contraction"] == 0
     ref = oracle_batch(oracle, prepared, samples, sp.log_priors_dla, sp.log_priors_no_dla)
     assert_parity(got, ref)
+
+
+def test_a_batch_whose_chunks_take_different_kernel_families(oracle):
+    """Masked quasars with the intended gather (config 3: gather != identity -> FP64 kernels) interleaved with unmasked
+    ones (config 1 -> int8 slice path), one quasar per chunk, inside ONE call: every quasar meets the gates, and equals
+    what it gives when the whole batch is one (FP64) chunk to rounding."""
+    S = 256
+    _, _, samples, sp3, prep3 = prepared_config("config3", 4, S, "intended")
+    _, _, samples1, sp1, prep1 = prepared_config("config1", 4, S, "intended")
+    assert np.array_equal(samples.nhi_samples, samples1.nhi_samples)
+    prepared = [p for pair in zip(prep3, prep1) for p in pair]
+    lpd = np.array([v for pair in zip(sp3.log_priors_dla, sp1.log_priors_dla) for v in pair])
+    lpn = np.array([v for pair in zip(sp3.log_priors_no_dla, sp1.log_priors_no_dla) for v in pair])
+    ident = [bool(np.array_equal(p.profile_index, np.arange(p.n))) for p in prepared]
+    assert ident == [False, True] * 4
+    split = _run(prepared, samples, 20, S, lpd, lpn, workspace_bytes=16 * 320 * 1232)
+    assert split["_timing"]["chunks"] == 8
+    ref = oracle_batch(oracle, prepared, samples, lpd, lpn)
+    assert_parity(split, ref)
+    whole = _run(prepared, samples, 20, S, lpd, lpn)
+    assert whole["_timing"]["chunks"] == 1 and whole["_timing"]["contraction"] == 0
+    assert np.max(np.abs(split["sample_log_likelihoods_dla"] - whole["sample_log_likelihoods_dla"])) <= 2e-9
+    assert np.array_equal(split["map_ind"], whole["map_ind"])
