@@ -36,6 +36,8 @@ NCU_K2_DRAM_GB_PER_QUASAR = (3.257835 + 0.006098) / 16
 # 16-quasar launch) and the FP64 instructions of the slice-emitting Voigt kernel per (hypothesis, pixel)
 NCU_K2S_DRAM_GB_PER_QUASAR = (2.894050 + 0.321743) / 16   # profiles/r02_ncu_slices_summary.txt
 NCU_K1S_FP64_PER_PIXEL = 56.84   # FP64-pipe warp instructions x 32 / (hypothesis, pixel) pairs, same file
+SLICE_PAIRS = 27                 # sample slices i < 6 x table slices j < 7 with i + j <= 6 (csrc/slices_path.cuh, NSA = 6)
+PLANE_BYTES_PER_PAIR = 12.0      # int8 planes of W and U per (hypothesis, pixel): 2 x 6 slices
 INT8_NOMINAL_TOPS = 4500.0       # dense 8-bit tensor peak NVIDIA quotes for B200 (= fp8)
 FP64_PIPE_TFLOPS = 37.1   # register-resident DMMA / DFMA loops, tools/probe_fp64.cu, profiles/r01_probe_fp64.jsonl
 # BASELINE.json configs as (rank, grid spacing, ragged masking, hypotheses); SURVEY.md 8(d)
@@ -422,19 +424,19 @@ def run_ours(args):
                     "launches_per_step": int(tm["chunks"]), "ms_per_step": 1e3 * t_contract,
                     "step_frac_end_to_end": step_tflops / dgemm_tflops}
     else:
-        # int8 slice contraction: 28 slice pairs x (224 + 32) columns x n_pad32 pixels x S_pad128 samples, 2 ops per MAC;
+        # int8 slice contraction: SLICE_PAIRS slice pairs x (224 + 32) columns x n_pad32 pixels x S_pad128 samples, 2 ops per MAC;
         # the tensor peak for 8-bit operands is twice the measured bf16 figure (same pipe, K = 32 instead of 16 per MMA)
         spad = (S + 1 + 127) // 128 * 128
         npad32 = float(((batch.n + 31) // 32 * 32).sum())
         gcols = slice_gcols(K_RANK)
-        int8_ops = 2.0 * 28 * gcols * spad * npad32
+        int8_ops = 2.0 * SLICE_PAIRS * gcols * spad * npad32
         # denominator: the burst figure (the sustained one is what cuBLAS bf16 reaches at ITS power draw, 1.24 GHz here;
         # the int8 contraction draws less per operation and runs at 1.7 GHz, so it can exceed twice the sustained figure)
         bf16_peak = float(peaks.get("bf16_tflops", 1650.0))
         int8_peak = 2.0 * bf16_peak
         int8_sustained = 2.0 * float(peaks.get("bf16_tflops_sustained", 1400.0))
         ach8 = int8_ops / t_contract / 1e12
-        roofline = {"kernel": "contract_slices_tiles_kernel (K2s: exact-slice int8 tcgen05 contraction, 7 x 7 slices, "
+        roofline = {"kernel": "contract_slices_tiles_kernel (K2s: exact-slice int8 tcgen05 contraction, 6 x 7 slices, "
                               "int32 TMEM accumulators, fp64 recombination)",
                     "bound": "tensor", "achieved": ach8, "peak": int8_peak, "unit": "TFLOP/s", "frac": ach8 / int8_peak,
                     "unit_note": "tensor-core operations per second on 8-bit integer operands (one multiply-add = 2), i.e. int8 TOP/s; "
@@ -453,7 +455,7 @@ def run_ours(args):
                                                 "cuBLAS DGEMM 8192^3 measured in this run: the contraction no longer runs on the FP64 pipe"},
                     "traffic": (NCU_K2S_DRAM_GB_PER_QUASAR * Q / max(1, tm["chunks"])) if args.workload == "config2" and S == 10000 and K_RANK == 20 else None,
                     "traffic_unit": "GB per launch (dram__bytes_read.sum + dram__bytes_write.sum of profiles/r02_ncu_slices_summary.txt, "
-                                    "scaled from its 16-quasar launch; algorithmic bytes: int8 planes of W and U 0.177 GB + G 0.021 GB per quasar)",
+                                    "scaled from its 16-quasar launch; algorithmic bytes: int8 planes of W and U 0.151 GB + G 0.021 GB per quasar)",
                     "launches_per_step": int(tm["chunks"]), "ms_per_step": 1e3 * t_contract,
                     "step_fp64_equivalent_vs_dgemm": step_tflops / dgemm_tflops}
     if slices:
@@ -467,7 +469,7 @@ def run_ours(args):
                           "peak_pipe": FP64_PIPE_TFLOPS, "unit": "TFLOP/s (2 x FP64 instructions)",
                           "frac": fl / t_voigt / 1e12 / dgemm_tflops, "frac_of_pipe": fl / t_voigt / 1e12 / FP64_PIPE_TFLOPS,
                           "fp64_instructions_per_hypothesis_pixel": NCU_K1S_FP64_PER_PIXEL,
-                          "plane_write_gbs": 14.0 * spad * npad32 / t_voigt / 1e9, "hbm_peak_gbs": hbm_peak,
+                          "plane_write_gbs": PLANE_BYTES_PER_PAIR * spad * npad32 / t_voigt / 1e9, "hbm_peak_gbs": hbm_peak,
                           "faddeeva_evals_per_s": 3.0 * S * float((batch.n_full + 6).sum()) / t_voigt,
                           "ms_per_step": 1e3 * t_voigt,
                           "peak_source": "cuBLAS DGEMM measured in this run; peak_pipe = DFMA/DMMA probe constant "

@@ -2,7 +2,7 @@
 //
 // For three lines and the as-written gather (any rank k <= 64), the Woodbury contraction of log_mvnpdf_low_rank.m:22 and
 // :26-28 leaves the FP64 pipe: the Voigt kernel emits W and U directly as seven signed 8-bit slices per value
-// (same bytes as fp64, minus one), the per-quasar table [Phi | M] is sliced once, and the products run on the
+// (six bytes per value instead of the eight of fp64), the per-quasar table [Phi | M] is sliced once, and the products run on the
 // integer tcgen05 path with int32 TMEM accumulators, one per slice diagonal.  Pipeline of a chunk of quasars:
 //
 //   pixel_scales_kernel      per-pixel power-of-two bounds c_w >= max w, c_u >= 2 max |u|          (K0s)
@@ -15,15 +15,15 @@
 //   chol_generic_kernel      the same for 20 < k <= 64 from the rows of G (kernels.cuh: shared memory, warp per sample)
 //
 // Fixed point.  Sample side: t = w / c_w in [0, 1) or t = u / c_u in (-1/2, 1/2) enters a double's mantissa by ONE
-// fma with a magic constant (1.0 / 1.5): X = round(t 2^52), two's complement.  The bytes of 16 X ARE the slices (a
-// funnel shift by four bits, so that the top slice carries eight significant bits instead of four and every kept slice
-// pair sits 16 x lower): 16 X = sum_i a_i 256^(6-i), a_1..a_6 plain unsigned bytes, a_0 the top byte -- unsigned for W
-// (t >= 0), signed for U; the MMAs of slice 0 of a U unit declare a signed A operand, all others an unsigned one.  So
-// t = sum_i a_i 2^(-8 i - 8) with no digit arithmetic at all.
-// Table side: b = entry / tau in [-1, 1] with 54 fractional bits in balanced digits b_j in [-128, 127],
+// fma with a magic constant (16.0 / 24.0): X = round(t 2^48), two's complement, in mantissa bits 0..47.  Its six bytes
+// ARE the slices: X = sum_i a_i 256^(5-i), a_1..a_5 plain unsigned bytes, a_0 the top byte -- unsigned for W (t >= 0),
+// signed for U; the MMAs of slice 0 of a U unit declare a signed A operand, all others an unsigned one.  So
+// t = sum_i a_i 2^(-8 i - 8) with no digit arithmetic at all, rounded at 2^-49 of the pixel's power-of-two scale.
+// (-DDLA_NSA=7: seven slices, the bytes of 16 round(t 2^52); 16 x finer, measured 5 % slower end to end.)
+// Table side: b = entry / tau in [-1, 1] with 54 fractional bits in seven balanced digits b_j in [-128, 127],
 // b = sum_j b_j 2^(-8 j - 6).  Slice products with i + j = d share the weight 2^(-8 d - 14) and accumulate exactly
 // in int32 (|sum| <= 7 * 2^15 * pixels < 2^31 for pixels <= 9 000); pairs with i + j >= 7 are dropped: at most
-// 6 * 2^-55 of the product of the two scales per pixel, rms 2^-55 -- below the 2^-53 rounding of the sample value itself.
+// 6 * 2^-55 of the product of the two scales per pixel -- far below the rounding of the sample value.
 #ifndef GPDLA_SLICES_PATH_CUH
 #define GPDLA_SLICES_PATH_CUH
 
@@ -32,8 +32,16 @@
 namespace dla {
 namespace sl {
 
-constexpr int NSL = 7;                         // slices per value
-constexpr int A_STEP7 = NSL * 2 * SB * 16;     // 28 672 bytes of sample planes per K step (32 pixels, 128 samples)
+constexpr int NSL = 7;                         // slices per table value = slice diagonals kept
+#ifndef DLA_NSA
+#define DLA_NSA 6
+#endif
+// Slices per sample value.  6 (default): X = round(t 2^48), its six bytes are the slices as they lie (sample values
+// rounded at 2^-49 of their power-of-two scale; 27 slice pairs).  7: X = round(t 2^52), the bytes of 16 X (28 pairs):
+// 16 x finer, +14 % plane bytes, +8 % MMA time (tuning build -DDLA_NSA=7; DESIGN.md 4b has both measured).
+constexpr int NSA = DLA_NSA;
+static_assert(NSA == 6 || NSA == 7, "sample slices: 6 or 7");
+constexpr int A_STEP7 = NSA * 2 * SB * 16;     // bytes of sample planes per K step (32 pixels, 128 samples): 24 576 (28 672)
 constexpr int B_STEP64 = NSL * 2 * 64 * 16;    // 14 336 bytes of table planes per K step, 64-column unit
 constexpr int B_STEP32 = NSL * 2 * 32 * 16;    //  7 168, 32-column unit
 constexpr int GCOLS = 256;                     // row of G: [0, 224) W.Phi (k (k+1) / 2 used), [224, 256) U.M (k used)
@@ -80,7 +88,7 @@ __host__ __device__ inline void unit_of_col(const SliceLayout& L, int c, int& co
     if (cu < 64 * L.u64) { col0 = L.voff + (cu & ~63); N = 64; } else { col0 = L.voff + 64 * L.u64; N = 32; }
   }
 }
-constexpr int K2S_STAGE = A_STEP7 + B_STEP64;  // 43 008
+constexpr int K2S_STAGE = A_STEP7 + B_STEP64;  // 38 912 (43 008)
 // ring depth of the contraction: 5 when it has the SM to itself, 3 (130 KB) when Voigt CTAs of the next chunk share it
 constexpr size_t k2s_smem(int stages) { return (size_t)stages * K2S_STAGE + 1024 + 256; }
 constexpr int K2S_THREADS = 320;               // warp 0 TMA producer, warp 1 MMA issue, warps 2..9 epilogue (two per TMEM lane quarter)
@@ -265,26 +273,36 @@ __global__ void table_slices_kernel(const QuasarDesc* __restrict__ desc, const S
 // 44..51), so bits(MAGIC) need not be subtracted: for W (MAGIC = 1.0) the mantissa is X itself; for U (MAGIC = 1.5)
 // it is X + 2^51, i.e. the two's-complement X with its sign bit flipped -- one xor on the top-slice word (TOPFLIP).
 template <bool TOPFLIP>
-__device__ __forceinline__ void digits4(const double (&m)[4], uint32_t (&out)[NSL]) {
+__device__ __forceinline__ void digits4(const double (&m)[4], uint32_t* out /* [NSA] */) {
   uint32_t lo[4], hi[4];
 #pragma unroll
   for (int h = 0; h < 4; ++h) {
     const uint32_t l = (uint32_t)__double2loint(m[h]), hh = (uint32_t)__double2hiint(m[h]);
-    lo[h] = l << 4;                         // 16 X: the top slice becomes bits 44..51 of X
-    hi[h] = __funnelshift_l(l, hh, 4);
+    if (NSA == 7) {
+      lo[h] = l << 4;                         // 16 X: the top slice becomes bits 44..51 of X
+      hi[h] = __funnelshift_l(l, hh, 4);
+    } else {
+      lo[h] = l;                              // X = round(t 2^48) sits in mantissa bits 0..47 as it is
+      hi[h] = hh;
+    }
   }
   const uint32_t t0 = __byte_perm(lo[0], lo[1], 0x5140), t1 = __byte_perm(lo[2], lo[3], 0x5140);
   const uint32_t t2 = __byte_perm(lo[0], lo[1], 0x7362), t3 = __byte_perm(lo[2], lo[3], 0x7362);
-  out[6] = __byte_perm(t0, t1, 0x5410);
-  out[5] = __byte_perm(t0, t1, 0x7632);
-  out[4] = __byte_perm(t2, t3, 0x5410);
-  out[3] = __byte_perm(t2, t3, 0x7632);
+  out[NSA - 1] = __byte_perm(t0, t1, 0x5410);
+  out[NSA - 2] = __byte_perm(t0, t1, 0x7632);
+  out[NSA - 3] = __byte_perm(t2, t3, 0x5410);
+  out[NSA - 4] = __byte_perm(t2, t3, 0x7632);
   const uint32_t t4 = __byte_perm(hi[0], hi[1], 0x5140), t5 = __byte_perm(hi[2], hi[3], 0x5140);
-  const uint32_t t6 = __byte_perm(hi[0], hi[1], 0x0062), t7 = __byte_perm(hi[2], hi[3], 0x0062);
-  out[2] = __byte_perm(t4, t5, 0x5410);
-  out[1] = __byte_perm(t4, t5, 0x7632);
-  out[0] = __byte_perm(t6, t7, 0x5410) ^ (TOPFLIP ? 0x80808080u : 0u);
+  out[NSA - 5] = __byte_perm(t4, t5, 0x5410);
+  out[NSA - 6] = __byte_perm(t4, t5, 0x7632);
+  if (NSA == 7) {
+    const uint32_t t6 = __byte_perm(hi[0], hi[1], 0x0062), t7 = __byte_perm(hi[2], hi[3], 0x0062);
+    // the mantissa of 1.5 + t is X + 2^51: two's-complement X with its sign bit flipped -- one xor on the top-slice word
+    out[0] = __byte_perm(t6, t7, 0x5410) ^ (TOPFLIP ? 0x80808080u : 0u);
+  }
 }
+constexpr double MAGIC_W = (NSA == 7) ? 1.0 : 16.0;   // ulp(MAGIC) = 2^-52 or 2^-48: the fma rounds t to that grid
+constexpr double MAGIC_U = (NSA == 7) ? 1.5 : 24.0;   // + 2^51 ulps: negative t stays in the same binade
 
 // MINB: resident CTAs per SM the kernel is compiled for (3 -> 162 registers; 4 -> 126, the default, no spills).  PXS: the per-pixel records
 // {omega2, noise, mu, flux, 1/c_w, 1/c_u} of the segment are staged in shared memory (px_cap pixels, 48 B each);
@@ -398,32 +416,35 @@ voigt_slices_lane_kernel(const QuasarDesc* __restrict__ desc, const SliceQuasar*
       double mw[4], mu_[4];
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
-        mw[h] = fma(w[h], is[h].x, 1.0);
-        mu_[h] = fma(u[h], is[h].y, 1.5);
+        mw[h] = fma(w[h], is[h].x, MAGIC_W);
+        mu_[h] = fma(u[h], is[h].y, MAGIC_U);
       }
-      uint32_t nw[NSL], nu[NSL];
+      uint32_t nw[NSA + 2], nu[NSA + 2];   // padded to two quads
+      nw[NSA] = nw[NSA + 1] = nu[NSA] = nu[NSA + 1] = 0u;
       digits4<false>(mw, nw);
       digits4<true>(mu_, nu);
       const int qs = g & 3;
       if (qs < 3) {
-        // slice quads {W0..W3}, {W4..W6, -}, {U0..U3}, {U4..U6, -}: four 16-byte stores per step instead of fourteen words
+        // slice quads {W0..W3}, {W4.., 0}, {U0..U3}, {U4.., 0}: four 16-byte stores per step instead of 2 NSA words
         uint4* slot = stg_s + qs * K1Q_THREADS;
         slot[0] = make_uint4(nw[0], nw[1], nw[2], nw[3]);
-        slot[3 * K1Q_THREADS] = make_uint4(nw[4], nw[5], nw[6], 0u);
+        slot[3 * K1Q_THREADS] = make_uint4(nw[4], nw[5], nw[6], nw[7]);
         slot[6 * K1Q_THREADS] = make_uint4(nu[0], nu[1], nu[2], nu[3]);
-        slot[9 * K1Q_THREADS] = make_uint4(nu[4], nu[5], nu[6], 0u);
+        slot[9 * K1Q_THREADS] = make_uint4(nu[4], nu[5], nu[6], nu[7]);
       } else {
         const int ch = g >> 2;
         const int64_t o = (int64_t)(ch >> 1) * A_STEP7 + (ch & 1) * (SB * 16);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const uint4 s0 = stg_s[(3 * q) * K1Q_THREADS], s1 = stg_s[(3 * q + 1) * K1Q_THREADS], s2 = stg_s[(3 * q + 2) * K1Q_THREADS];
-          int8_t* dst = ((q < 2) ? wq : uq) + o + (q & 1) * 4 * (2 * SB * 16);
+          constexpr int PL = 2 * SB * 16;   // bytes of one slice plane of a K step
+          int8_t* dst = ((q < 2) ? wq : uq) + o + (q & 1) * 4 * PL;
           const uint32_t* last = ((q < 2) ? nw : nu) + (q & 1) * 4;
+          const int sl0 = (q & 1) * 4;
           *reinterpret_cast<uint4*>(dst) = make_uint4(s0.x, s1.x, s2.x, last[0]);
-          *reinterpret_cast<uint4*>(dst + (2 * SB * 16)) = make_uint4(s0.y, s1.y, s2.y, last[1]);
-          *reinterpret_cast<uint4*>(dst + 2 * (2 * SB * 16)) = make_uint4(s0.z, s1.z, s2.z, last[2]);
-          if ((q & 1) == 0) *reinterpret_cast<uint4*>(dst + 3 * (2 * SB * 16)) = make_uint4(s0.w, s1.w, s2.w, last[3]);
+          *reinterpret_cast<uint4*>(dst + PL) = make_uint4(s0.y, s1.y, s2.y, last[1]);
+          if (sl0 + 2 < NSA) *reinterpret_cast<uint4*>(dst + 2 * PL) = make_uint4(s0.z, s1.z, s2.z, last[2]);
+          if (sl0 + 3 < NSA) *reinterpret_cast<uint4*>(dst + 3 * PL) = make_uint4(s0.w, s1.w, s2.w, last[3]);
         }
       }
     }
@@ -490,7 +511,7 @@ __device__ __forceinline__ void k2s_issue_step(uint32_t abase, uint32_t bbase, u
   const uint32_t a_lo = ((abase >> 4) & 0x3FFFu) | ((uint32_t)((SB * 16) >> 4) << 16);
   const uint32_t b_lo = ((bbase >> 4) & 0x3FFFu) | ((uint32_t)((NSL * 16 * N) >> 4) << 16);
 #pragma unroll
-  for (int i = 0; i < NSL; ++i) {
+  for (int i = 0; i < NSA; ++i) {
     const uint64_t ad = HI | (uint64_t)(a_lo + (uint32_t)(i * ((2 * SB * 16) >> 4)));
     const int ntot = (NSL - i) * N;
 #pragma unroll

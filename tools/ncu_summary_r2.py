@@ -71,10 +71,10 @@ with open("profiles/r02_ncu_slices_summary.txt", "w") as f:
                     f"all instructions {v['inst'] * 32 / pairs:.1f} per pair\n")
     for name, v in facts.items():
         if "contract_slices" in name:
-            ops = 2.0 * 28 * 256 * pairs
-            f.write(f"  K2s: int8 operations 2 x 28 slice pairs x 256 columns x pairs = {ops:.4g}; / {v['time']} ms = {ops / v['time'] / 1e9:.0f} TOP/s; "
+            ops = 2.0 * 27 * 256 * pairs
+            f.write(f"  K2s: int8 operations 2 x 27 slice pairs x 256 columns x pairs = {ops:.4g}; / {v['time']} ms = {ops / v['time'] / 1e9:.0f} TOP/s; "
                     f"tensor pipe active {v['tensor_pct']:.1f} % of cycles; DRAM {v['dram_read'] + v['dram_write']:.3f} GB per launch against "
-                    f"algorithmic planes {14 * pairs / 1e9:.3f} GB + tables + G {16 * 10112 * 256 * 8 / 1e9:.3f} GB\n")
+                    f"algorithmic planes {12 * pairs / 1e9:.3f} GB + tables + G {16 * 10112 * 256 * 8 / 1e9:.3f} GB\n")
     f.write(json.dumps(facts) + "\n")
 print(open("profiles/r02_ncu_slices_summary.txt").read())
 
