@@ -34,8 +34,8 @@ N_PIX, K_RANK = 1217, 20
 NCU_K2_DRAM_GB_PER_QUASAR = (3.257835 + 0.006098) / 16
 # the same for the int8 slice contraction (profiles/r02_ncu_slices_summary.txt: 2.919 GB read + 0.325 GB written by one
 # 16-quasar launch) and the FP64 instructions of the slice-emitting Voigt kernel per (hypothesis, pixel)
-NCU_K2S_DRAM_GB_PER_QUASAR = (2.894050 + 0.321743) / 16   # profiles/r02_ncu_slices_summary.txt
-NCU_K1S_FP64_PER_PIXEL = 56.84   # FP64-pipe warp instructions x 32 / (hypothesis, pixel) pairs, same file
+NCU_K2S_DRAM_GB_PER_QUASAR = (2.469627 + 0.321808) / 16   # profiles/r02_ncu_slices_summary.txt
+NCU_K1S_FP64_PER_PIXEL = 56.84   # DFMA + DMUL + DADD warp instructions x 32 / (hypothesis, pixel) pairs (ncu source page by opcode)
 SLICE_PAIRS = 27                 # sample slices i < 6 x table slices j < 7 with i + j <= 6 (csrc/slices_path.cuh, NSA = 6)
 PLANE_BYTES_PER_PAIR = 12.0      # int8 planes of W and U per (hypothesis, pixel): 2 x 6 slices
 INT8_NOMINAL_TOPS = 4500.0       # dense 8-bit tensor peak NVIDIA quotes for B200 (= fp8)
